@@ -1,0 +1,176 @@
+/*
+ * seqalign_b200.h -- C ABI of libseqalign_b200.so
+ *
+ * B200-native (sm_100a) replacement for ONE hot path of jakovdev/SequenceAligner:
+ * the score-only all-vs-all pairwise DP fill (Needleman-Wunsch linear gap, Gotoh
+ * global affine, Smith-Waterman local affine) over every i<j pair of a sequence
+ * set.  Plain pointers and sizes only; no C++ / torch types cross this boundary.
+ *
+ * What each entry point replaces in the reference (paths under the reference
+ * repo root):
+ *
+ *   sab_device_count / sab_device_memory
+ *        <- cuda_device_init + cuda_memory   src/interface/seqalign_cuda.c:48-93
+ *   sab_create
+ *        <- `struct constants C` fill + cudaMemcpyToSymbol
+ *                                            src/interface/seqalign_cuda.c:115-125,168
+ *           (method selection = ALIGN->kernel / ALIGN->gap, src/bio/align.h:28-38)
+ *   sab_upload
+ *        <- cudaMalloc/cudaMemcpy of letters + meta
+ *                                            src/interface/seqalign_cuda.c:127-132
+ *   sab_align / sab_align_shard
+ *        <- the batched launch + D2H loop    src/interface/seqalign_cuda.c:134-294
+ *           and, semantically, align() + output_fill()
+ *                                            src/bio/align.c:21-72, src/io/output.c:68-84
+ *   sab_filter
+ *        <- filter() decisions               src/bio/filter.c:14-62 (sequential -T 1 semantics)
+ *   sab_matrix_lookup
+ *        <- parse_matrix                     src/bio/matrices.c:44-57
+ *
+ * The reference-signature shim on top of this ABI (`bool cuda_align(struct input,
+ * struct output)`, `bool cuda_memory(size_t)`, src/interface/seqalign_cuda.h:7-9)
+ * is in sequencealigner_b200/csrc/seqalign_shim.cpp; INTEGRATION.md shows how a
+ * reference maintainer links it.
+ *
+ * There is NO CPU fallback: every compute entry point fails with
+ * SAB_ERR_NODEVICE / SAB_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef SEQALIGN_B200_H
+#define SEQALIGN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SAB_ABI_VERSION 1
+
+enum sab_status {
+	SAB_OK = 0,
+	SAB_ERR_ARG = -1, /* bad argument / unsupported configuration */
+	SAB_ERR_NODEVICE = -2, /* no usable CUDA device */
+	SAB_ERR_CUDA = -3, /* CUDA runtime error, see sab_last_error */
+	SAB_ERR_NOMEM = -4, /* host or device allocation failed */
+	SAB_ERR_STATE = -5, /* call order violated (e.g. align before upload) */
+	SAB_ERR_OVERFLOW = -6, /* int16 re-run list overflowed (internal, retried) */
+};
+
+/* src/bio/method/{nw,ga,sw}.c */
+enum sab_method { SAB_NW = 0, SAB_GA = 1, SAB_SW = 2 };
+
+/* == struct meta, src/bio/align.h:6-9 */
+typedef struct sab_meta {
+	int32_t off; /* byte offset of the sequence in `seqs` */
+	int32_t len; /* letters, excluding the terminating NUL */
+} sab_meta;
+
+enum sab_flags {
+	SAB_FLAG_FORCE_INT32 = 1, /* testing: never use the packed int16x2 kernels */
+	SAB_FLAG_FORCE_INT16 = 2, /* testing: skip the a-priori range test (SW still re-runs) */
+};
+
+typedef struct sab_config {
+	int32_t method; /* enum sab_method */
+	int32_t gap_pen; /* <= 0, linear (GAP_PEN, src/bio/align.c:14)  */
+	int32_t gap_open; /* <= 0, affine (GAP_OPN, src/bio/align.c:15)  */
+	int32_t gap_ext; /* <= 0, affine (GAP_EXT, src/bio/align.c:16)  */
+	int32_t seq_lut[128]; /* SEQ_LUT, ASCII -> index or -1 (src/bio/matrices.c:12) */
+	int32_t sub_mat[24 * 24]; /* SUB_MAT, must be symmetric (src/bio/matrices.c:13) */
+	int32_t device; /* CUDA device ordinal this context drives */
+	int32_t panel; /* sequences per panel, multiple of 32; 0 = auto */
+	int32_t flags; /* enum sab_flags */
+	int32_t reserved[5];
+} sab_config;
+
+typedef struct sab_stats {
+	double kernel_ms; /* CUDA-event time of the alignment kernels of the last sab_align* */
+	double total_ms; /* wall time of the last sab_align* call */
+	double upload_ms; /* wall time of the last sab_upload */
+	int64_t pairs; /* pairs scored by the last sab_align* call */
+	int64_t cells; /* sum of len_i*len_j over those pairs */
+	int64_t rerun_pairs; /* pairs re-scored in int32 after int16 overflow */
+	int64_t launches; /* kernels launched by the last sab_align* call */
+	int64_t tiles; /* panel tiles processed */
+	int64_t tiles_int32; /* panel tiles routed wholesale to the int32 kernel */
+	int64_t h2d_bytes; /* bytes copied host->device by the last sab_upload */
+	int64_t d2h_bytes; /* bytes copied device->host by the last sab_align* */
+	int64_t reserved[5];
+} sab_stats;
+
+typedef struct sab_ctx sab_ctx;
+
+/* Called from the thread that called sab_align*, between tiles. */
+typedef void (*sab_progress_fn)(int64_t pairs_done, int64_t pairs_total, void *user);
+
+int sab_abi_version(void);
+
+/* Number of usable CUDA devices (0 when none / driver missing). */
+int sab_device_count(void);
+/* cudaMemGetInfo of `device`. */
+int sab_device_memory(int device, size_t *free_bytes, size_t *total_bytes);
+
+int sab_create(sab_ctx **ctx, const sab_config *cfg);
+void sab_destroy(sab_ctx *ctx);
+const char *sab_last_error(const sab_ctx *ctx);
+
+/*
+ * Hands the host sequence store to the device: `seqs` holds `num` uppercase
+ * ASCII sequences, NUL-terminated, back to back; meta[k] locates sequence k;
+ * `max` is the longest length (== struct input, src/io/input.h:6-11).  The
+ * letters are mapped through seq_lut, length-binned (stable sort inside each
+ * panel) and packed into the two device layouts of DESIGN.md section 3.  The
+ * host buffers are not referenced after return.
+ */
+int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t num,
+	       int32_t max);
+
+/*
+ * Scores every pair i<j and fills the caller-owned host matrix exactly like
+ * output_fill (src/io/output.c:68-84):
+ *   triangular != 0 : matrix[j(j-1)/2 + i] = score(i,j)       (length num(num-1)/2)
+ *   triangular == 0 : matrix[num*i+j] = matrix[num*j+i] = score(i,j); the
+ *                     diagonal is not written.
+ * matrix == NULL computes (and keeps the scores in device memory) but copies
+ * nothing back, like the reference's -W / --no-write (seqalign_cuda.c:233).
+ * `matrix` may be pageable or a file-backed MAP_SHARED mapping: it is only
+ * written with plain host stores from this call's worker threads.
+ */
+int sab_align(sab_ctx *ctx, int32_t *matrix, int triangular, sab_progress_fn progress,
+	      void *user);
+
+/*
+ * Multi-GPU: the panel-tile list of the job is split into `nshards`
+ * cost-balanced shards; this call computes shard `shard` on this context's
+ * device and writes only that shard's cells of `matrix` (disjoint between
+ * shards, so several contexts/threads/processes can fill one matrix, or each
+ * its own).  sab_align == shard 0 of 1.
+ */
+int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matrix,
+		    int triangular, sab_progress_fn progress, void *user);
+
+int sab_get_stats(const sab_ctx *ctx, sab_stats *out);
+
+/*
+ * Redundancy filter decisions (src/bio/filter.c:14-62, the deterministic
+ * sequential semantics): lost[j] = 1 iff some KEPT i<j has
+ * (float)matches/(float)min(len_i,len_j) >= threshold over the common prefix.
+ * Works on the raw letters given here (independent of sab_upload).  Returns the
+ * number of lost sequences (>= 0) or a negative sab_status.
+ */
+int sab_filter(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t num,
+	       float threshold, uint8_t *lost);
+
+/* Built-in substitution tables (host only, no device needed). */
+int sab_matrix_count(void);
+const char *sab_matrix_name(int index);
+/* Fills SEQ_LUT / SUB_MAT for table `name` (case-insensitive, src/bio/matrices.c:47).
+ * Returns SAB_OK or SAB_ERR_ARG. */
+int sab_matrix_lookup(const char *name, int32_t seq_lut[128], int32_t sub_mat[24 * 24]);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* SEQALIGN_B200_H */
