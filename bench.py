@@ -1,0 +1,392 @@
+#!/usr/bin/env python3
+"""bench.py -- all-vs-all GCUPS of the B200 path (BASELINE.json metric) + CPU reference arm.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c2]
+
+One "step" = one full pass of the hot path (score every i<j pair) over the synthetic
+workload.  N=1 runs BASELINE.json configs[1] (C2: 10 000 proteins, len U{250..350},
+`-a ga -m blosum62 -s 10 -e 1`).  For N>1 (torchrun, one rank per GPU) the pair space is
+sharded by row strips with no data-path collective; the sequence count grows with sqrt(N)
+so the pairs per GPU stay fixed ("weak").
+
+JSON keys (one line, rank 0):
+  value      GCUPS, inputs resident in HBM, scores left in HBM (-W mode), device time
+             (CUDA events recorded by the library on its own streams), max over ranks
+  e2e        GCUPS through the C ABI with HOST buffers: sab_upload (pack + H2D) and
+             sab_align into a host matrix (D2H + host scatter) inside the timed region
+  roofline   dominant kernel vs the integer-pipe peak measured on this box
+             (tools/pipe_peak.cu); HBM shown non-binding next to it
+  cpu_baseline  the reference's own CPU code (oracle/_ref/seqalign) on this box's host
+             cores, bounded sample of the same workload
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+# algorithmic integer lane-instructions per DP cell
+INSTR_PER_CELL = {"nw": 1.5, "ga": 3.0, "sw": 3.5}
+# what the kernels actually issue per cell on the integer pipes
+EXEC_INSTR_PER_CELL = {"nw": 1.5, "ga": 2.5, "sw": 2.75}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), \
+        int(os.environ.get("WORLD_SIZE", 1))
+
+
+def reduce_over_ranks(ms: float, units: int):
+    """max of the per-rank times, sum of the per-rank unit counts (no-op for one rank)."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return float(ms), int(units)
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    u = torch.tensor([units], dtype=torch.int64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.all_reduce(u, op=dist.ReduceOp.SUM)
+    return float(t.item()), int(u.item())
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.path = index, None, None
+
+    def __enter__(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "200"], stdout=f,
+                stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+        return self
+
+    def __exit__(self, *exc):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self):
+        if not self.path or not os.path.exists(self.path):
+            return None
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            p = [x.strip() for x in line.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0]))
+                mx = max(mx, float(p[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.path)
+        if not sm:
+            return None
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": mx, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def workload(config: str, n_gpus: int, n_override: int | None):
+    from sequencealigner_b200 import AlignConfig, synth
+    base = synth.CONFIGS[config]
+    n = n_override or int(round(base["n"] * np.sqrt(n_gpus)))
+    store, c = synth.make(config, n=n)
+    cfg = AlignConfig(c["method"], c["matrix"], gap_pen=c.get("gap_pen"),
+                      gap_open=c.get("gap_open"), gap_ext=c.get("gap_ext"))
+    desc = {"workload": f"{config}: synthetic {'DNA' if c['alphabet'] == 'ACGT' else 'protein'} "
+                        f"{n} seqs len {c['lo']}..{c['hi']}, -a {c['method']} -m {c['matrix']} "
+                        + (f"-p {c['gap_pen']}" if "gap_pen" in c else
+                           f"-s {c['gap_open']} -e {c['gap_ext']}"),
+            "sequences": n, "pairs": store.pairs(), "cells": store.cells(),
+            "seed": c["seed"], "layout": "packed-triangular int32"}
+    return store, cfg, c, desc
+
+
+# ---------------------------------------------------------------------------------------
+# CPU reference arm / baseline
+# ---------------------------------------------------------------------------------------
+
+def cpu_reference_sample(store, c, target_s: float = 15.0):
+    """Times the reference's own CPU alignment (oracle/_ref/seqalign, all host threads) on
+    the first M sequences of the workload, M sized for ~target_s of CPU work.  Falls back
+    to the oracle port (liboracle.so, OpenMP) when the reference binary is not there."""
+    from oracle import oracle
+    cores = os.cpu_count() or 1
+    cli = oracle.ref_args(c["method"], c["matrix"], gap_pen=c.get("gap_pen"),
+                          gap_open=c.get("gap_open"), gap_ext=c.get("gap_ext"))
+
+    def run(m):
+        sub = store.head(m)
+        if oracle.ref_available():
+            with tempfile.TemporaryDirectory() as td:
+                fa = Path(td) / "sample.fasta"
+                sub.to_fasta(fa)
+                r = oracle.run_reference(fa, cli, threads=0, write=False, bench=True)
+            secs = r["align_seconds"]
+            if not secs or secs <= 0:
+                raise RuntimeError("could not read 'Alignment: X sec' from the reference")
+            return sub.cells(), secs, "reference"
+        from sequencealigner_b200 import AlignConfig
+        r = AlignConfig(c["method"], c["matrix"], gap_pen=c.get("gap_pen"),
+                        gap_open=c.get("gap_open"), gap_ext=c.get("gap_ext")).resolve()
+        t0 = time.perf_counter()
+        cells = oracle.time_columns(r, sub, 1, sub.num)
+        return cells, time.perf_counter() - t0, "port"
+
+    mean_len = float(store.lengths.mean())
+    m0 = int(min(store.num, max(64, np.sqrt(2 * 4e9 / mean_len ** 2))))  # ~4e9 cells probe
+    cells, secs, kind = run(m0)
+    rate = cells / max(secs, 1e-3)
+    m = int(min(store.num, max(m0, np.sqrt(2 * rate * target_s / mean_len ** 2))))
+    if m > m0 * 1.3:
+        cells, secs, kind = run(m)
+    else:
+        m = m0
+    return {"value": cells / secs / 1e9, "unit": "GCUPS", "cores": cores, "kind": kind,
+            "sample": f"first {m} of {store.num} sequences ({cells:.3e} cells, {secs:.2f} s "
+                      f"alignment time, threads=all)", "_cells": cells, "_secs": secs, "_m": m}
+
+
+def run_reference_arm(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return 0
+    store, cfg, c, desc = workload(args.config, args.gpus, args.n)
+    per_step = max(4.0, min(20.0, 150.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_reference_sample(store, c, target_s=per_step)
+    cells = secs = 0.0
+    last = None
+    for _ in range(args.steps):
+        last = cpu_reference_sample(store, c, target_s=per_step)
+        cells += last["_cells"]
+        secs += last["_secs"]
+    value = cells / secs / 1e9
+    base = {k: v for k, v in last.items() if not k.startswith("_")}
+    base["value"] = value
+    out = {"impl": "reference", "metric": "all-vs-all GCUPS", "value": value, "unit": "GCUPS",
+           "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": desc,
+           "cpu_baseline": base,
+           "e2e": {"value": value, "unit": "GCUPS", "h2d_bytes_per_step": 0,
+                   "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------
+
+def measure_pipe_peak(device: int):
+    import ctypes as C
+    from sequencealigner_b200.build import PIPE_LIB
+    if not PIPE_LIB.exists():
+        return None
+    lib = C.CDLL(str(PIPE_LIB))
+    lib.sab_pipe_peak.restype = C.c_int
+    lib.sab_pipe_peak.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    names = {0: "viaddmnmx_s16x2", 1: "vimnmx3_s16x2", 2: "viadd_16x2", 3: "iadd3", 4: "imad",
+             5: "lds32", 6: "ga_mix_alu", 7: "ga_mix_alu_fma", 8: "viaddmnmx_u16x2",
+             9: "vimnmx3_u16x2"}
+    out = {}
+    for op, name in names.items():
+        g, ms = C.c_double(), C.c_double()
+        if lib.sab_pipe_peak(op, device, C.byref(g), C.byref(ms)) == 0:
+            out[name] = g.value / 1e3  # tera lane-instr/s
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from sequencealigner_b200 import Aligner
+
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the alignment path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    n_gpus = world
+
+    store, cfg, c, desc = workload(args.config, n_gpus, args.n)
+    desc["parallelism"] = f"row-strip shards x{n_gpus}, no collective"
+    desc["l2_flush"] = "512 MiB device memset between timed steps"
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    al = Aligner(cfg, device=local_rank, shards_hint=n_gpus)
+    al.upload(store)
+    n = store.num
+    host_matrix = np.zeros(n * (n - 1) // 2, dtype=np.int32)
+
+    # ---- device-resident throughput (`value`) ------------------------------------------
+    for _ in range(args.warmup):
+        al.align(write=False, shard=rank, nshards=world)
+    dev_ms, my_cells, launches = 0.0, 0, 0
+    kernel_ms = 0.0
+    barrier()
+    with ClockSampler(local_rank) as clocks:
+        t_wall0 = time.perf_counter()
+        for _ in range(args.steps):
+            flush.zero_()
+            torch.cuda.synchronize()
+            al.align(write=False, shard=rank, nshards=world)
+            st = al.stats()
+            dev_ms += st["device_ms"]
+            kernel_ms += st["kernel_ms"]
+            my_cells += st["cells"]
+            launches += st["launches"]
+        barrier()
+        wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    clk = clocks.summary()
+    step_ms, step_cells = reduce_over_ranks(dev_ms / args.steps, my_cells // args.steps)
+    value = step_cells / (step_ms * 1e-3) / 1e9
+    kern_step_ms, _ = reduce_over_ranks(kernel_ms / args.steps, 0)
+
+    # ---- end to end through the C ABI with host buffers (`e2e`) ------------------------
+    for _ in range(min(args.warmup, 1)):
+        al.upload(store)
+        al.align(out=host_matrix, shard=rank, nshards=world)
+    barrier()
+    e2e_t0 = time.perf_counter()
+    h2d = d2h = 0
+    for _ in range(args.steps):
+        al.upload(store)
+        al.align(out=host_matrix, shard=rank, nshards=world)
+        st = al.stats()
+        h2d, d2h = st["h2d_bytes"], st["d2h_bytes"]
+        launches += st["launches"]
+    barrier()
+    e2e_ms = (time.perf_counter() - e2e_t0) * 1e3 / args.steps
+    e2e_ms, _ = reduce_over_ranks(e2e_ms, 0)
+    e2e_value = step_cells / (e2e_ms * 1e-3) / 1e9
+    checksum = int(host_matrix.astype(np.int64).sum())
+    al.close()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel (sab_tile_kernel<method, int16x2>) ------------
+    peaks = measure_pipe_peak(local_rank) or {}
+    method = c["method"]
+    alu_peak = max(peaks.get("viaddmnmx_s16x2", 0.0), peaks.get("vimnmx3_s16x2", 0.0)) or None
+    cells_per_s_gpu = step_cells / n_gpus / (kern_step_ms * 1e-3)
+    achieved = cells_per_s_gpu * INSTR_PER_CELL[method] / 1e12
+    traffic = None
+    tf = ROOT / "profiles" / "traffic.json"
+    if tf.exists():
+        try:
+            traffic = json.loads(tf.read_text()).get(f"{args.config}_bytes_per_launch")
+        except (ValueError, OSError):
+            traffic = None
+    measured = {}
+    mp = ROOT / "MEASURED_PEAKS.json"
+    if mp.exists():
+        try:
+            measured = json.loads(mp.read_text())
+        except ValueError:
+            measured = {}
+    hbm_peak = float(measured.get("hbm_gbs", 6650.0))
+    bits = 5 if c["alphabet"] != "ACGT" else 2
+    alg_bytes = float(store.pairs()) * 4 + float(store.lengths.sum()) * bits / 8 * 2
+    roofline = {
+        "bound": "int_alu", "kernel": f"sab_tile_kernel<{method},int16x2>",
+        "achieved": achieved, "peak": alu_peak, "unit": "T lane-instr/s",
+        "frac": (achieved / alu_peak) if alu_peak else None,
+        "peak_source": "measured on this box by tools/pipe_peak.cu (DPX VIADDMNMX/VIMNMX3 "
+                       "issue rate, all SMs); MEASURED_PEAKS.json has no integer figure",
+        "instr_per_cell_algorithmic": INSTR_PER_CELL[method],
+        "instr_per_cell_issued": EXEC_INSTR_PER_CELL[method],
+        "gcups_kernel_per_gpu": cells_per_s_gpu / 1e9,
+        "pipe_peaks_T_lane_instr_s": peaks,
+        "traffic": traffic,
+        "hbm": {"algorithmic_bytes_per_step": alg_bytes,
+                "achieved_gbs": alg_bytes / n_gpus / (kern_step_ms * 1e-3) / 1e9,
+                "peak_gbs": hbm_peak,
+                "peak_source": "MEASURED_PEAKS.json" if measured else "fallback",
+                "note": "non-binding"},
+    }
+
+    cpu = None
+    if n_gpus == 1 and not args.no_cpu:
+        cpu = cpu_reference_sample(store, c, target_s=args.cpu_seconds)
+        cpu = {k: v for k, v in cpu.items() if not k.startswith("_")}
+
+    out = {
+        "metric": "all-vs-all GCUPS", "value": value, "unit": "GCUPS", "n_gpus": n_gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16x2",
+        "data": "synthetic", "config": desc,
+        "pairs_per_s": desc["pairs"] / (step_ms * 1e-3),
+        "wall_ms_per_step": wall_ms / args.steps,
+        "e2e": {"value": e2e_value, "unit": "GCUPS", "ms_per_step": e2e_ms,
+                "pairs_per_s": desc["pairs"] / (e2e_ms * 1e-3),
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "checksum": checksum},
+        "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+    }
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5"])
+    ap.add_argument("--n", type=int, default=None, help="override the sequence count")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    args = ap.parse_args()
+    if args.steps < 1:
+        raise SystemExit("--steps must be >= 1")
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -81,11 +81,17 @@ typedef struct sab_config {
 	int32_t device; /* CUDA device ordinal this context drives */
 	int32_t panel; /* sequences per panel, multiple of 32; 0 = auto */
 	int32_t flags; /* enum sab_flags */
-	int32_t reserved[5];
+	int32_t shards_hint; /* how many shards sab_align_shard will be called with (sizes the
+			      * auto panel so every shard gets several row strips); 0 = 1 */
+	int32_t reserved[4];
 } sab_config;
 
 typedef struct sab_stats {
-	double kernel_ms; /* CUDA-event time of the alignment kernels of the last sab_align* */
+	double kernel_ms; /* device time covered by the alignment kernels of the last sab_align*
+			   * (union of the per-strip CUDA-event intervals; strips overlap) */
+	double busy_ms; /* sum of the per-strip kernel durations */
+	double device_ms; /* CUDA-event time from the first kernel's start to the end of all
+			   * device work of the call (kernels, re-runs, D2H), gaps included */
 	double total_ms; /* wall time of the last sab_align* call */
 	double upload_ms; /* wall time of the last sab_upload */
 	int64_t pairs; /* pairs scored by the last sab_align* call */
@@ -96,7 +102,7 @@ typedef struct sab_stats {
 	int64_t tiles_int32; /* panel tiles routed wholesale to the int32 kernel */
 	int64_t h2d_bytes; /* bytes copied host->device by the last sab_upload */
 	int64_t d2h_bytes; /* bytes copied device->host by the last sab_align* */
-	int64_t reserved[5];
+	int64_t reserved[3];
 } sab_stats;
 
 typedef struct sab_ctx sab_ctx;
@@ -149,6 +155,18 @@ int sab_align(sab_ctx *ctx, int32_t *matrix, int triangular, sab_progress_fn pro
  */
 int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matrix,
 		    int triangular, sab_progress_fn progress, void *user);
+
+/* Row strips of the job (fixed by sab_upload): strip k covers original rows
+ * [row0, row0 + rows).  sab_strip_owner tells which shard computes it, so a
+ * multi-process host knows which rows of `matrix` each rank filled. */
+int sab_strip_count(const sab_ctx *ctx);
+/* Host only (no device needed): the same plan computed from the lengths alone.
+ * panel = 0 sizes the panel for `nshards` shards (== sab_config.shards_hint = nshards).
+ * Returns the number of strips; fills at most max_strips entries. */
+int sab_plan_strips(const sab_meta *meta, int32_t num, int32_t panel, int32_t nshards,
+		    int32_t max_strips, int32_t *row0, int32_t *rows, int32_t *owner);
+int sab_strip_info(const sab_ctx *ctx, int32_t strip, int32_t nshards, int32_t *row0,
+		   int32_t *rows, int32_t *owner);
 
 int sab_get_stats(const sab_ctx *ctx, sab_stats *out);
 

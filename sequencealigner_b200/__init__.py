@@ -1,0 +1,9 @@
+"""sequencealigner_b200 -- B200-native (sm_100a) score-only all-vs-all pairwise
+alignment (Needleman-Wunsch, Gotoh, Smith-Waterman), drop-in for that one path of
+jakovdev/SequenceAligner.  The product is libseqalign_b200.so (C ABI:
+include/seqalign_b200.h); this package is the Python host binding around it."""
+from .aligner import AlignConfig, Aligner, align_all, matrix_lookup, matrix_names  # noqa: F401
+from .seqstore import SeqStore, read_fasta  # noqa: F401
+
+__all__ = ["AlignConfig", "Aligner", "align_all", "matrix_lookup", "matrix_names", "SeqStore",
+           "read_fasta"]

@@ -1,0 +1,1006 @@
+// sab_capi.cu -- C ABI of libseqalign_b200.so (include/seqalign_b200.h).
+//
+// Host side of the B200 score-only all-vs-all path: context, upload packing
+// (length-binned SoA), row-strip scheduling over the triangular pair space,
+// launch of the sm_100a kernels (sab_kernels.cuh) and tiled write-back into the
+// caller's similarity matrix.  Replaces the reference's device backend
+// (reference: src/interface/seqalign_cuda.c:95-296) -- one launch per row strip
+// instead of 64 Mi-pair linear batches, nothing N^2-sized is required on the
+// device beyond two strip buffers.
+//
+// There is no CPU fallback in this file: without a usable sm_100 device every
+// compute entry point returns SAB_ERR_NODEVICE / SAB_ERR_CUDA.
+#include "sab_internal.h"
+#include "sab_kernels.cuh"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <numeric>
+#include <string>
+#include <thread>
+#include <vector>
+
+namespace {
+
+using sab::DeviceSeqs;
+using sab::TileParams;
+
+constexpr int kPanelQuantum = sab::kThreads; // panels are multiples of the query block
+constexpr size_t kStageBytes = 32u << 20; // pinned bounce buffer (x2)
+constexpr unsigned kRerunCap = 1u << 20;
+constexpr int kRerunThreads = 4096;
+
+double now_ms()
+{
+	using namespace std::chrono;
+	return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+inline int64_t tri(int64_t j)
+{
+	return j * (j - 1) / 2; // == alignments(j), reference: src/util/macros.h:13
+}
+
+struct StripBuf {
+	int32_t *blk = nullptr;
+	int32_t *blkT = nullptr;
+	size_t blk_cap = 0, blkT_cap = 0; // elements
+	uint2 *bnd = nullptr;
+	size_t bnd_cap = 0;
+	unsigned *counter = nullptr; // [0] work counter, [1] rerun count
+	unsigned long long *rerun_list = nullptr;
+	int32_t *rerun_scratch = nullptr;
+	size_t rerun_scratch_cap = 0;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev_start = nullptr, ev_done = nullptr;
+};
+
+} // namespace
+
+struct sab_ctx {
+	sab_config cfg{};
+	std::string err;
+	int sm_count = 0;
+	// scoring
+	int32_t sub25[sab::kLetters * sab::kLetters]{};
+	int min_s = 0, max_s = 0;
+	int gapA = 0, gapE = 0;
+	int32_t *d_sub25 = nullptr;
+	// sequence store (host copies of the small tables)
+	bool uploaded = false;
+	int32_t num = 0, max_len = 0, panel = 0;
+	std::vector<int32_t> slot_len, slot_orig;
+	std::vector<int64_t> len_prefix; // len_prefix[s] = sum of slot_len[0..s)
+	std::vector<int32_t> panel_maxlen;
+	int32_t *d_slot_len = nullptr, *d_slot_orig = nullptr;
+	int64_t *d_col_off = nullptr, *d_grp_off = nullptr;
+	uint8_t *d_col_bytes = nullptr;
+	uint32_t *d_rowpack = nullptr;
+	// execution
+	StripBuf buf[2];
+	void *stage[2] = { nullptr, nullptr };
+	cudaStream_t copy_stream = nullptr;
+	cudaEvent_t ev_copy[2] = { nullptr, nullptr };
+	cudaEvent_t ev_span[2] = { nullptr, nullptr }; // first kernel start / last kernel end
+	int grid_blocks[3][2]{}; // [method][packed] resident persistent blocks
+	sab_stats stats{};
+};
+
+namespace {
+
+int fail(sab_ctx *c, int code, const char *fmt, ...)
+{
+	char b[512];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(b, sizeof b, fmt, ap);
+	va_end(ap);
+	if (c)
+		c->err = b;
+	return code;
+}
+
+#define CU(call)                                                                              \
+	do {                                                                                  \
+		cudaError_t e_ = (call);                                                      \
+		if (e_ != cudaSuccess)                                                        \
+			return fail(ctx, e_ == cudaErrorMemoryAllocation ? SAB_ERR_NOMEM :    \
+									   SAB_ERR_CUDA,      \
+				    "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__,  \
+				    __LINE__);                                                \
+	} while (0)
+
+typedef void (*tile_kernel_t)(const TileParams);
+
+tile_kernel_t pick_kernel(int method, bool packed)
+{
+	switch (method * 2 + (packed ? 1 : 0)) {
+	case 0: return sab::sab_tile_kernel<sab::M_NW, false>;
+	case 1: return sab::sab_tile_kernel<sab::M_NW, true>;
+	case 2: return sab::sab_tile_kernel<sab::M_GA, false>;
+	case 3: return sab::sab_tile_kernel<sab::M_GA, true>;
+	case 4: return sab::sab_tile_kernel<sab::M_SW, false>;
+	default: return sab::sab_tile_kernel<sab::M_SW, true>;
+	}
+}
+
+void free_seqs(sab_ctx *c)
+{
+	cudaFree(c->d_slot_len);
+	cudaFree(c->d_slot_orig);
+	cudaFree(c->d_col_off);
+	cudaFree(c->d_grp_off);
+	cudaFree(c->d_col_bytes);
+	cudaFree(c->d_rowpack);
+	c->d_slot_len = c->d_slot_orig = nullptr;
+	c->d_col_off = c->d_grp_off = nullptr;
+	c->d_col_bytes = nullptr;
+	c->d_rowpack = nullptr;
+	c->uploaded = false;
+}
+
+void free_bufs(sab_ctx *c)
+{
+	for (auto &b : c->buf) {
+		cudaFree(b.blk);
+		cudaFree(b.blkT);
+		cudaFree(b.bnd);
+		cudaFree(b.rerun_scratch);
+		b.blk = b.blkT = nullptr;
+		b.bnd = nullptr;
+		b.rerun_scratch = nullptr;
+		b.blk_cap = b.blkT_cap = b.bnd_cap = b.rerun_scratch_cap = 0;
+	}
+}
+
+// Parallel host copy of one staged chunk into the (pageable, possibly file-backed)
+// destination matrix: plain stores only (SURVEY section 8b "Output").
+struct Seg {
+	int32_t *dst;
+	const int32_t *src;
+	size_t n;
+};
+
+void copy_segments(const std::vector<Seg> &segs)
+{
+	size_t total = 0;
+	for (auto &s : segs)
+		total += s.n;
+	unsigned hw = std::thread::hardware_concurrency();
+	int nthreads = (int)std::min<size_t>(std::max(1u, std::min(hw, 8u)), total / (1u << 18) + 1);
+	if (nthreads <= 1) {
+		for (auto &s : segs)
+			memcpy(s.dst, s.src, s.n * sizeof(int32_t));
+		return;
+	}
+	// split by element count
+	const size_t per = (total + nthreads - 1) / nthreads;
+	std::vector<std::thread> th;
+	for (int t = 0; t < nthreads; t++) {
+		th.emplace_back([&, t]() {
+			size_t lo = per * t, hi = std::min(total, lo + per), pos = 0;
+			for (auto &s : segs) {
+				size_t b = std::max(lo, pos), e = std::min(hi, pos + s.n);
+				if (b < e)
+					memcpy(s.dst + (b - pos), s.src + (b - pos),
+					       (e - b) * sizeof(int32_t));
+				pos += s.n;
+				if (pos >= hi)
+					break;
+			}
+		});
+	}
+	for (auto &t : th)
+		t.join();
+}
+
+// A-priori int16 range test for a strip.  lq/ls are the
+// longest query / subject of the strip; the DP is swept over subject columns
+// padded to the register-strip width.
+bool int16_safe(const sab_ctx *c, int lq, int ls)
+{
+	const int64_t lsp = ((int64_t)ls + sab::kStrip - 1) / sab::kStrip * sab::kStrip;
+	const int64_t gA = c->gapA, gE = c->gapE;
+	const int64_t hi = (int64_t)std::min<int64_t>(lq, lsp) * std::max(c->max_s, 0);
+	int64_t lo;
+	switch (c->cfg.method) {
+	case SAB_NW: lo = (lq + lsp + 2) * gA; break;
+	case SAB_GA: lo = 2 * gA + (lq + lsp) * gE; break;
+	default: lo = 0; break;
+	}
+	// stored values: M + gapA, Y >= M + gapA, transient Y + gapE, diag + (S - gapA)
+	const int64_t low = lo + gA + gE + std::min(c->min_s, 0);
+	const int64_t high = (c->cfg.method == SAB_SW ? 0 : hi) + std::max(c->max_s, 0) - gA;
+	// profile entries S - gapA and the SW threshold arithmetic must fit as well
+	if (c->max_s - gA > 16000 || c->min_s - gA < -16000 || -gA > 8000 || -gE > 8000)
+		return false;
+	return low >= -32000 && high <= 32000;
+}
+
+// Panel height: a multiple of the query block; several strips per shard so the LPT
+// assignment balances, capped so a block's 128 length-sorted queries stay similar.
+int auto_panel(int num, int panel, int shards_hint)
+{
+	if (panel > 0)
+		return panel;
+	const int want = shards_hint > 0 ? 6 * shards_hint : 6;
+	panel = (num / want + kPanelQuantum - 1) / kPanelQuantum * kPanelQuantum;
+	return std::max(2 * kPanelQuantum, std::min(panel, 4096));
+}
+
+// Longest-processing-time assignment of strips (cost ~ cells) to shards; deterministic.
+void lpt_assign(const std::vector<double> &cost, int nshards, std::vector<int> &owner)
+{
+	const int n = (int)cost.size();
+	std::vector<int> order(n);
+	std::iota(order.begin(), order.end(), 0);
+	std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return cost[x] > cost[y]; });
+	std::vector<double> load(nshards, 0.0);
+	owner.assign(n, 0);
+	for (int idx : order) {
+		int best = 0;
+		for (int k = 1; k < nshards; k++)
+			if (load[k] < load[best])
+				best = k;
+		load[best] += cost[idx];
+		owner[idx] = best;
+	}
+}
+
+bool int32_safe(const sab_ctx *c, int lq, int ls)
+{
+	const int64_t lsp = (int64_t)ls + sab::kStrip;
+	const int64_t gA = c->gapA, gE = c->gapE;
+	const int64_t hi = (int64_t)std::min<int64_t>(lq, lsp) * std::max(c->max_s, 0) - gA;
+	int64_t lo = (c->cfg.method == SAB_NW) ? (lq + lsp + 2) * gA : 2 * gA + (lq + lsp) * gE;
+	lo += gA + gE + std::min(c->min_s, 0);
+	return hi < (1ll << 29) && lo > -(1ll << 29);
+}
+
+} // namespace
+
+int sab_internal_device(const sab_ctx *ctx)
+{
+	return ctx && ctx->sm_count ? ctx->cfg.device : -1;
+}
+
+int sab_internal_fail(sab_ctx *ctx, int code, const char *fmt, ...)
+{
+	char b[512];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(b, sizeof b, fmt, ap);
+	va_end(ap);
+	if (ctx)
+		ctx->err = b;
+	return code;
+}
+
+extern "C" {
+
+int sab_abi_version(void)
+{
+	return SAB_ABI_VERSION;
+}
+
+int sab_device_count(void)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) {
+		cudaGetLastError();
+		return 0;
+	}
+	int usable = 0;
+	for (int d = 0; d < n; d++) {
+		cudaDeviceProp p;
+		if (cudaGetDeviceProperties(&p, d) == cudaSuccess && p.major == 10)
+			usable++;
+	}
+	return usable;
+}
+
+int sab_device_memory(int device, size_t *free_bytes, size_t *total_bytes)
+{
+	int cur = 0;
+	if (cudaGetDevice(&cur) != cudaSuccess || cudaSetDevice(device) != cudaSuccess) {
+		cudaGetLastError();
+		return SAB_ERR_NODEVICE;
+	}
+	size_t f = 0, t = 0;
+	cudaError_t e = cudaMemGetInfo(&f, &t);
+	cudaSetDevice(cur);
+	if (e != cudaSuccess)
+		return SAB_ERR_CUDA;
+	if (free_bytes)
+		*free_bytes = f;
+	if (total_bytes)
+		*total_bytes = t;
+	return SAB_OK;
+}
+
+const char *sab_last_error(const sab_ctx *ctx)
+{
+	return ctx ? ctx->err.c_str() : "null context";
+}
+
+int sab_create(sab_ctx **out, const sab_config *cfg)
+{
+	if (!out || !cfg)
+		return SAB_ERR_ARG;
+	*out = nullptr;
+	sab_ctx *ctx = new (std::nothrow) sab_ctx;
+	if (!ctx)
+		return SAB_ERR_NOMEM;
+	*out = ctx; // returned even on failure so sab_last_error works; caller destroys
+	ctx->cfg = *cfg;
+	if (cfg->method < SAB_NW || cfg->method > SAB_SW)
+		return fail(ctx, SAB_ERR_ARG, "unknown method %d", cfg->method);
+	if (cfg->gap_pen > 0 || cfg->gap_open > 0 || cfg->gap_ext > 0)
+		return fail(ctx, SAB_ERR_ARG, "gap values must be stored <= 0 (align.c:127)");
+	if (cfg->panel < 0 || cfg->panel % kPanelQuantum)
+		return fail(ctx, SAB_ERR_ARG, "panel must be a multiple of %d", kPanelQuantum);
+	ctx->gapA = cfg->method == SAB_NW ? cfg->gap_pen : cfg->gap_open;
+	ctx->gapE = cfg->method == SAB_NW ? 0 : cfg->gap_ext;
+	// symmetric tables only (all 67 reference tables are; the kernels swap the
+	// operand order freely between nw.c:27 and ga.c:46)
+	int mn = INT32_MAX, mx = INT32_MIN;
+	for (int a = 0; a < 24; a++)
+		for (int b = 0; b < 24; b++) {
+			const int v = cfg->sub_mat[a * 24 + b];
+			if (v != cfg->sub_mat[b * 24 + a])
+				return fail(ctx, SAB_ERR_ARG, "substitution matrix is not symmetric");
+			mn = std::min(mn, v);
+			mx = std::max(mx, v);
+		}
+	ctx->min_s = mn;
+	ctx->max_s = mx;
+	if ((int64_t)mx - mn > (1 << 20) || -(int64_t)ctx->gapA > (1 << 28) ||
+	    -(int64_t)ctx->gapE > (1 << 28))
+		return fail(ctx, SAB_ERR_ARG, "scores out of the supported int32 range");
+	for (int a = 0; a < sab::kLetters; a++)
+		for (int b = 0; b < sab::kLetters; b++) {
+			const int v = (a < 24 && b < 24) ? cfg->sub_mat[a * 24 + b] : 0;
+			ctx->sub25[a * sab::kLetters + b] = v - ctx->gapA;
+		}
+
+	int ndev = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+		cudaGetLastError();
+		return fail(ctx, SAB_ERR_NODEVICE, "no CUDA device (this library has no CPU fallback)");
+	}
+	if (cfg->device < 0 || cfg->device >= ndev)
+		return fail(ctx, SAB_ERR_NODEVICE, "device %d out of range (%d present)", cfg->device,
+			    ndev);
+	cudaDeviceProp prop;
+	CU(cudaGetDeviceProperties(&prop, cfg->device));
+	if (prop.major != 10)
+		return fail(ctx, SAB_ERR_NODEVICE,
+			    "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device,
+			    prop.major, prop.minor);
+	CU(cudaSetDevice(cfg->device));
+	ctx->sm_count = prop.multiProcessorCount;
+	CU(cudaMalloc(&ctx->d_sub25, sizeof ctx->sub25));
+	CU(cudaMemcpy(ctx->d_sub25, ctx->sub25, sizeof ctx->sub25, cudaMemcpyHostToDevice));
+	for (int m = 0; m < 3; m++)
+		for (int pk = 0; pk < 2; pk++) {
+			tile_kernel_t k = pick_kernel(m, pk);
+			CU(cudaFuncSetAttribute((const void *)k,
+						cudaFuncAttributeMaxDynamicSharedMemorySize,
+						sab::kSmemBytes));
+			int occ = 0;
+			CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)k,
+									 sab::kThreads, sab::kSmemBytes));
+			if (occ < 1)
+				return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
+			ctx->grid_blocks[m][pk] = occ * ctx->sm_count;
+		}
+	for (int i = 0; i < 2; i++) {
+		StripBuf &b = ctx->buf[i];
+		CU(cudaStreamCreateWithFlags(&b.stream, cudaStreamNonBlocking));
+		CU(cudaEventCreate(&b.ev_start));
+		CU(cudaEventCreate(&b.ev_done));
+		CU(cudaMalloc(&b.counter, 4 * sizeof(unsigned)));
+		CU(cudaMalloc(&b.rerun_list, sizeof(unsigned long long) * kRerunCap));
+		CU(cudaHostAlloc(&ctx->stage[i], kStageBytes, cudaHostAllocDefault));
+		CU(cudaEventCreateWithFlags(&ctx->ev_copy[i], cudaEventDisableTiming));
+	}
+	CU(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+	CU(cudaEventCreate(&ctx->ev_span[0]));
+	CU(cudaEventCreate(&ctx->ev_span[1]));
+	return SAB_OK;
+}
+
+void sab_destroy(sab_ctx *ctx)
+{
+	if (!ctx)
+		return;
+	if (ctx->sm_count) {
+		cudaSetDevice(ctx->cfg.device);
+		cudaDeviceSynchronize();
+		free_seqs(ctx);
+		free_bufs(ctx);
+		cudaFree(ctx->d_sub25);
+		for (int i = 0; i < 2; i++) {
+			StripBuf &b = ctx->buf[i];
+			cudaFree(b.counter);
+			cudaFree(b.rerun_list);
+			if (b.stream)
+				cudaStreamDestroy(b.stream);
+			if (b.ev_start)
+				cudaEventDestroy(b.ev_start);
+			if (b.ev_done)
+				cudaEventDestroy(b.ev_done);
+			if (ctx->stage[i])
+				cudaFreeHost(ctx->stage[i]);
+			if (ctx->ev_copy[i])
+				cudaEventDestroy(ctx->ev_copy[i]);
+		}
+		if (ctx->copy_stream)
+			cudaStreamDestroy(ctx->copy_stream);
+		for (auto e : ctx->ev_span)
+			if (e)
+				cudaEventDestroy(e);
+		cudaGetLastError();
+	}
+	delete ctx;
+}
+
+int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t num, int32_t max)
+{
+	if (!ctx)
+		return SAB_ERR_ARG;
+	if (!ctx->sm_count)
+		return fail(ctx, SAB_ERR_STATE, "context has no device");
+	if (!seqs || !meta || num < 2)
+		return fail(ctx, SAB_ERR_ARG, "need at least 2 sequences (SEQ_N_MIN, align.h:21)");
+	const double t0 = now_ms();
+	CU(cudaSetDevice(ctx->cfg.device));
+	free_seqs(ctx);
+
+	int32_t real_max = 0;
+	int64_t letters = 0;
+	for (int32_t k = 0; k < num; k++) {
+		if (meta[k].len < 1 || meta[k].off < 0)
+			return fail(ctx, SAB_ERR_ARG, "sequence %d has bad length/offset", k);
+		real_max = std::max(real_max, meta[k].len);
+		letters += meta[k].len;
+	}
+	if (max > 0 && max < real_max)
+		return fail(ctx, SAB_ERR_ARG, "max (%d) is below the longest sequence (%d)", max,
+			    real_max);
+	if (!int32_safe(ctx, real_max, real_max))
+		return fail(ctx, SAB_ERR_ARG, "lengths x scores exceed the int32 score range");
+
+	// Panels: contiguous ranges of ORIGINAL indices, so a row strip of the output is
+	// one contiguous run of the packed-triangular matrix.
+	const int panel = auto_panel(num, ctx->cfg.panel, ctx->cfg.shards_hint);
+	const int npanels = (num + panel - 1) / panel;
+
+	// Length binning: stable sort by length inside each panel -> slots.
+	std::vector<int32_t> slot_orig(num), slot_len(num);
+	std::iota(slot_orig.begin(), slot_orig.end(), 0);
+	std::vector<int32_t> panel_maxlen(npanels, 0);
+	for (int p = 0; p < npanels; p++) {
+		auto b = slot_orig.begin() + (size_t)p * panel;
+		auto e = slot_orig.begin() + std::min<size_t>((size_t)(p + 1) * panel, num);
+		std::stable_sort(b, e, [&](int32_t x, int32_t y) { return meta[x].len < meta[y].len; });
+		panel_maxlen[p] = meta[*(e - 1)].len;
+	}
+	std::vector<int64_t> col_off(num), len_prefix(num + 1);
+	int64_t off = 0;
+	for (int32_t s = 0; s < num; s++) {
+		slot_len[s] = meta[slot_orig[s]].len;
+		col_off[s] = off;
+		len_prefix[s] = off;
+		off += slot_len[s];
+	}
+	len_prefix[num] = off;
+
+	// Subject layout: one byte per residue, index 0..23.
+	std::vector<uint8_t> col_bytes((size_t)letters + 16, 24);
+	for (int32_t s = 0; s < num; s++) {
+		const uint8_t *src = seqs + meta[slot_orig[s]].off;
+		uint8_t *dst = col_bytes.data() + col_off[s];
+		for (int32_t k = 0; k < slot_len[s]; k++) {
+			const uint8_t ch = src[k];
+			const int32_t idx = ch < 128 ? ctx->cfg.seq_lut[ch] : -1;
+			if (idx < 0 || idx >= 24)
+				return fail(ctx, SAB_ERR_ARG,
+					    "sequence %d has a letter outside the matrix alphabet",
+					    slot_orig[s]);
+			dst[k] = (uint8_t)idx;
+		}
+	}
+	// Query layout: 32-slot groups, 4 residues per word (stored as byte offsets
+	// letter*4 into a profile column), lane-interleaved for coalesced loads.
+	const int ngroups = (num + 31) / 32;
+	std::vector<int64_t> grp_off(ngroups);
+	int64_t rows4 = 0;
+	for (int g = 0; g < ngroups; g++) {
+		grp_off[g] = rows4;
+		const int last = std::min(num, (g + 1) * 32) - 1;
+		int gmax = 0;
+		for (int s = g * 32; s <= last; s++)
+			gmax = std::max(gmax, slot_len[s]);
+		rows4 += (gmax + 3) / 4 + 2; // + prefetch slack
+	}
+	std::vector<uint32_t> rowpack((size_t)rows4 * 32, 0);
+	for (int32_t s = 0; s < num; s++) {
+		const uint8_t *src = col_bytes.data() + col_off[s];
+		uint32_t *dst = rowpack.data() + grp_off[s >> 5] * 32 + (s & 31);
+		for (int32_t r = 0; r < slot_len[s]; r++)
+			dst[(size_t)(r >> 2) * 32] |= (uint32_t)(src[r] * 4) << (8 * (r & 3));
+	}
+
+	CU(cudaMalloc(&ctx->d_slot_len, sizeof(int32_t) * num));
+	CU(cudaMalloc(&ctx->d_slot_orig, sizeof(int32_t) * num));
+	CU(cudaMalloc(&ctx->d_col_off, sizeof(int64_t) * num));
+	CU(cudaMalloc(&ctx->d_grp_off, sizeof(int64_t) * ngroups));
+	CU(cudaMalloc(&ctx->d_col_bytes, col_bytes.size()));
+	CU(cudaMalloc(&ctx->d_rowpack, rowpack.size() * sizeof(uint32_t)));
+	CU(cudaMemcpy(ctx->d_slot_len, slot_len.data(), sizeof(int32_t) * num, cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_slot_orig, slot_orig.data(), sizeof(int32_t) * num,
+		      cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_col_off, col_off.data(), sizeof(int64_t) * num, cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_grp_off, grp_off.data(), sizeof(int64_t) * ngroups,
+		      cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_col_bytes, col_bytes.data(), col_bytes.size(), cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_rowpack, rowpack.data(), rowpack.size() * sizeof(uint32_t),
+		      cudaMemcpyHostToDevice));
+
+	ctx->num = num;
+	ctx->max_len = real_max;
+	ctx->panel = panel;
+	ctx->slot_len.swap(slot_len);
+	ctx->slot_orig.swap(slot_orig);
+	ctx->len_prefix.swap(len_prefix);
+	ctx->panel_maxlen.swap(panel_maxlen);
+	ctx->uploaded = true;
+	ctx->stats.upload_ms = now_ms() - t0;
+	ctx->stats.h2d_bytes = (int64_t)(sizeof(int32_t) * 2 * num + sizeof(int64_t) * (num + ngroups) +
+					 col_bytes.size() + rowpack.size() * sizeof(uint32_t));
+	return SAB_OK;
+}
+
+// Strip bookkeeping ------------------------------------------------------------------------
+
+namespace {
+
+struct Strip {
+	int panel; // index
+	int a0, an; // original index range == slot range
+	double cost; // sum len_q * sum len_s (approx. cells)
+	bool packed;
+	int lq, ls; // longest query / subject
+};
+
+int ensure(sab_ctx *ctx, void **p, size_t *cap, size_t need, size_t elem)
+{
+	if (need <= *cap)
+		return SAB_OK;
+	cudaFree(*p);
+	*p = nullptr;
+	*cap = 0;
+	cudaError_t e = cudaMalloc(p, need * elem);
+	if (e != cudaSuccess)
+		return fail(ctx, SAB_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", need * elem,
+			    cudaGetErrorString(e));
+	*cap = need;
+	return SAB_OK;
+}
+
+// Row strips (one per panel), their cost, and the longest-processing-time assignment
+// of strips to shards (deterministic: every rank computes the same plan).
+void plan_strips(const sab_ctx *ctx, int nshards, std::vector<Strip> &strips, std::vector<int> &owner)
+{
+	const int num = ctx->num, panel = ctx->panel;
+	const int npanels = (num + panel - 1) / panel;
+	const bool force32 = ctx->cfg.flags & SAB_FLAG_FORCE_INT32;
+	const bool force16 = ctx->cfg.flags & SAB_FLAG_FORCE_INT16;
+	strips.assign(npanels, Strip{});
+	int run_max = 0;
+	for (int p = 0; p < npanels; p++) {
+		Strip &s = strips[p];
+		s.panel = p;
+		s.a0 = p * panel;
+		s.an = std::min(panel, num - s.a0);
+		run_max = std::max(run_max, ctx->panel_maxlen[p]);
+		s.lq = ctx->panel_maxlen[p];
+		s.ls = run_max;
+		const double lq_sum = (double)(ctx->len_prefix[s.a0 + s.an] - ctx->len_prefix[s.a0]);
+		const double ls_sum = (double)ctx->len_prefix[s.a0] + 0.5 * lq_sum;
+		s.cost = lq_sum * ls_sum;
+		s.packed = !force32 && (force16 || int16_safe(ctx, s.lq, s.ls));
+	}
+	std::vector<double> cost(npanels);
+	for (int p = 0; p < npanels; p++)
+		cost[p] = strips[p].cost;
+	lpt_assign(cost, nshards, owner);
+}
+
+// Copies the finished strip (device) into the caller's matrix through the two pinned
+// bounce buffers.  tri: the strip IS matrix[tri(a0) .. tri(a0+an)).  full: lower-row
+// parts from blk, mirrored parts from blkT (output_fill, src/io/output.c:72-78).
+int drain_strip(sab_ctx *ctx, const Strip &st, StripBuf &b, int32_t *matrix, int triangular)
+{
+	const int64_t N = ctx->num;
+	const int64_t a0 = st.a0, a1 = st.a0 + st.an;
+	const size_t stage_elems = kStageBytes / sizeof(int32_t);
+	// pass 0 = lower rows (blk), pass 1 = mirror (blkT); two chunks in flight.
+	int slot = 0;
+	bool pending[2] = { false, false };
+	std::vector<Seg> pend_segs[2];
+	auto flush_slot = [&](int s) -> int {
+		if (!pending[s])
+			return SAB_OK;
+		CU(cudaEventSynchronize(ctx->ev_copy[s]));
+		copy_segments(pend_segs[s]);
+		pending[s] = false;
+		return SAB_OK;
+	};
+	auto submit = [&](const int32_t *dev, size_t n, std::vector<Seg> &&segs) -> int {
+		int rc = flush_slot(slot);
+		if (rc)
+			return rc;
+		CU(cudaMemcpyAsync(ctx->stage[slot], dev, n * sizeof(int32_t), cudaMemcpyDeviceToHost,
+				   ctx->copy_stream));
+		CU(cudaEventRecord(ctx->ev_copy[slot], ctx->copy_stream));
+		ctx->stats.d2h_bytes += (int64_t)(n * sizeof(int32_t));
+		pend_segs[slot] = std::move(segs);
+		pending[slot] = true;
+		slot ^= 1;
+		return SAB_OK;
+	};
+
+	// lower rows
+	{
+		const int64_t total = tri(a1) - tri(a0);
+		int64_t e = 0;
+		int64_t row = a0; // row containing element e
+		while (e < total) {
+			const size_t n = (size_t)std::min<int64_t>(stage_elems, total - e);
+			const int32_t *stage = (const int32_t *)ctx->stage[slot];
+			std::vector<Seg> segs;
+			if (triangular) {
+				segs.push_back({ matrix + tri(a0) + e, stage, n });
+			} else {
+				// rows overlapping [e, e+n)
+				int64_t pos = e;
+				while (pos < e + (int64_t)n) {
+					while (tri(row + 1) - tri(a0) <= pos)
+						row++;
+					const int64_t rbeg = tri(row) - tri(a0);
+					const int64_t col = pos - rbeg;
+					const int64_t cnt = std::min<int64_t>(row - col, e + n - pos);
+					if (cnt > 0)
+						segs.push_back({ matrix + row * N + col, stage + (pos - e),
+								 (size_t)cnt });
+					pos += cnt > 0 ? cnt : 1;
+				}
+			}
+			int rc = submit(b.blk + e, n, std::move(segs));
+			if (rc)
+				return rc;
+			e += n;
+		}
+	}
+	if (!triangular) {
+		// mirror: blkT[lo * an + (hi - a0)], lo in [0, a1); valid columns hi > lo
+		const int64_t an = st.an;
+		const int64_t rows_per = std::max<int64_t>(1, stage_elems / an);
+		for (int64_t lo0 = 0; lo0 < a1 - 1; lo0 += rows_per) {
+			const int64_t lo1 = std::min<int64_t>(a1 - 1, lo0 + rows_per);
+			const int32_t *stage = (const int32_t *)ctx->stage[slot];
+			std::vector<Seg> segs;
+			for (int64_t lo = lo0; lo < lo1; lo++) {
+				const int64_t h0 = std::max<int64_t>(a0, lo + 1);
+				segs.push_back({ matrix + lo * N + h0, stage + (lo - lo0) * an + (h0 - a0),
+						 (size_t)(a1 - h0) });
+			}
+			int rc = submit(b.blkT + lo0 * an, (size_t)((lo1 - lo0) * an), std::move(segs));
+			if (rc)
+				return rc;
+		}
+	}
+	int rc = flush_slot(0);
+	if (rc)
+		return rc;
+	return flush_slot(1);
+}
+
+} // namespace
+
+int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matrix, int triangular,
+		    sab_progress_fn progress, void *user)
+{
+	if (!ctx)
+		return SAB_ERR_ARG;
+	if (!ctx->uploaded)
+		return fail(ctx, SAB_ERR_STATE, "sab_upload must precede sab_align");
+	if (nshards < 1 || shard < 0 || shard >= nshards)
+		return fail(ctx, SAB_ERR_ARG, "bad shard %d of %d", shard, nshards);
+	CU(cudaSetDevice(ctx->cfg.device));
+	const double t0 = now_ms();
+	const int num = ctx->num;
+	const int method = ctx->cfg.method;
+	std::vector<Strip> strips;
+	std::vector<int> owner, mine;
+	plan_strips(ctx, nshards, strips, owner);
+	{ // costliest strips first: the tail of the job is then made of the cheap ones
+		std::vector<int> order(strips.size());
+		std::iota(order.begin(), order.end(), 0);
+		std::stable_sort(order.begin(), order.end(),
+				 [&](int x, int y) { return strips[x].cost > strips[y].cost; });
+		for (int idx : order)
+			if (owner[idx] == shard)
+				mine.push_back(idx);
+	}
+	int64_t pairs_total = 0;
+	for (int idx : mine)
+		pairs_total += tri(strips[idx].a0 + strips[idx].an) - tri(strips[idx].a0);
+
+	sab_stats &S = ctx->stats;
+	const double up_ms = S.upload_ms;
+	const int64_t h2d = S.h2d_bytes;
+	memset(&S, 0, sizeof S);
+	S.upload_ms = up_ms;
+	S.h2d_bytes = h2d;
+
+	DeviceSeqs dseqs{ ctx->d_slot_len, ctx->d_slot_orig, ctx->d_col_off, ctx->d_col_bytes,
+			  ctx->d_grp_off, ctx->d_rowpack };
+	const int bnd_rows = (ctx->max_len + 8 + 3) / 4 * 4;
+	int64_t pairs_done = 0;
+	std::vector<std::pair<float, float>> spans; // kernel intervals on the device timeline
+
+	auto launch = [&](const Strip &st, StripBuf &b) -> int {
+		const bool packed = st.packed;
+		const int grid = ctx->grid_blocks[method][packed];
+		const int a1 = st.a0 + st.an;
+		const size_t blk_elems = (size_t)(tri(a1) - tri(st.a0));
+		int rc = ensure(ctx, (void **)&b.blk, &b.blk_cap, std::max<size_t>(blk_elems, 1),
+				sizeof(int32_t));
+		if (rc)
+			return rc;
+		if (!triangular && matrix) {
+			rc = ensure(ctx, (void **)&b.blkT, &b.blkT_cap, (size_t)a1 * st.an,
+				    sizeof(int32_t));
+			if (rc)
+				return rc;
+		}
+		const size_t bnd_block = (size_t)(sab::kThreads / 32) * bnd_rows * 32;
+		rc = ensure(ctx, (void **)&b.bnd, &b.bnd_cap, bnd_block * grid, sizeof(uint2));
+		if (rc)
+			return rc;
+		TileParams p{};
+		p.seqs = dseqs;
+		p.a_slot0 = st.a0;
+		p.a_n = st.an;
+		p.a_orig0 = st.a0;
+		p.blk = b.blk;
+		p.tri0 = tri(st.a0);
+		p.blkT = (!triangular && matrix) ? b.blkT : nullptr;
+		p.chunk = packed ? 16 : 8;
+		p.nqb = (st.an + sab::kThreads - 1) / sab::kThreads;
+		p.nsc = (a1 + p.chunk - 1) / p.chunk;
+		p.counter = b.counter;
+		p.bnd = b.bnd;
+		p.bnd_block_stride = (int64_t)bnd_block;
+		p.bnd_rows = bnd_rows;
+		p.sub25 = ctx->d_sub25;
+		p.gapA = ctx->gapA;
+		p.gapE = ctx->gapE;
+		// SW a-posteriori test: while every M <= 32767 - max(S) the next diagonal step
+		// cannot wrap, so a wrapped pair always shows a running maximum above it first.
+		p.ovf_threshold = 32767 - std::max(ctx->max_s, 0);
+		p.rerun_list = b.rerun_list;
+		p.rerun_count = b.counter + 1;
+		p.rerun_cap = kRerunCap;
+		CU(cudaMemsetAsync(b.counter, 0, 4 * sizeof(unsigned), b.stream));
+		if (S.launches == 0)
+			CU(cudaEventRecord(ctx->ev_span[0], b.stream));
+		CU(cudaEventRecord(b.ev_start, b.stream));
+		pick_kernel(method, packed)<<<grid, sab::kThreads, sab::kSmemBytes, b.stream>>>(p);
+		CU(cudaGetLastError());
+		CU(cudaEventRecord(b.ev_done, b.stream));
+		S.launches++;
+		S.tiles++;
+		if (!packed)
+			S.tiles_int32++;
+		return SAB_OK;
+	};
+
+	auto finish = [&](const Strip &st, StripBuf &b) -> int {
+		CU(cudaEventSynchronize(b.ev_done));
+		float t_s = 0.f, t_e = 0.f;
+		CU(cudaEventElapsedTime(&t_s, ctx->ev_span[0], b.ev_start));
+		CU(cudaEventElapsedTime(&t_e, ctx->ev_span[0], b.ev_done));
+		if (method == SAB_SW && st.packed) {
+			unsigned cnt = 0;
+			CU(cudaMemcpyAsync(&cnt, b.counter + 1, sizeof cnt, cudaMemcpyDeviceToHost,
+					   b.stream));
+			CU(cudaStreamSynchronize(b.stream));
+			if (cnt > kRerunCap)
+				return fail(ctx, SAB_ERR_OVERFLOW,
+					    "int16 re-run list overflowed (%u pairs); use "
+					    "SAB_FLAG_FORCE_INT32",
+					    cnt);
+			if (cnt) {
+				const int cols = ctx->max_len + 1;
+				int rc = ensure(ctx, (void **)&b.rerun_scratch, &b.rerun_scratch_cap,
+						(size_t)kRerunThreads * 2 * cols, sizeof(int32_t));
+				if (rc)
+					return rc;
+				sab::RerunParams rp{};
+				rp.seqs = dseqs;
+				rp.list = b.rerun_list;
+				rp.count = b.counter + 1;
+				rp.cap = kRerunCap;
+				rp.scratch = b.rerun_scratch;
+				rp.scratch_cols = cols;
+				rp.sub25 = ctx->d_sub25;
+				rp.gapA = ctx->gapA;
+				rp.gapE = ctx->gapE;
+				rp.a_orig0 = st.a0;
+				rp.a_n = st.an;
+				rp.blk = b.blk;
+				rp.tri0 = tri(st.a0);
+				rp.blkT = (!triangular && matrix) ? b.blkT : nullptr;
+				sab::sab_rerun_sw_kernel<<<kRerunThreads / 128, 128, 0, b.stream>>>(rp);
+				CU(cudaGetLastError());
+				CU(cudaEventRecord(b.ev_done, b.stream));
+				CU(cudaEventSynchronize(b.ev_done));
+				CU(cudaEventElapsedTime(&t_e, ctx->ev_span[0], b.ev_done));
+				S.launches++;
+				S.rerun_pairs += cnt;
+			}
+		}
+		spans.push_back({ t_s, t_e });
+		if (matrix) {
+			int rc = drain_strip(ctx, st, b, matrix, triangular);
+			if (rc)
+				return rc;
+		}
+		const int a1 = st.a0 + st.an;
+		const int64_t np = tri(a1) - tri(st.a0);
+		pairs_done += np;
+		S.pairs += np;
+		if (progress)
+			progress(pairs_done, pairs_total, user);
+		return SAB_OK;
+	};
+
+	for (size_t k = 0; k < mine.size(); k++) {
+		int rc = launch(strips[mine[k]], ctx->buf[k & 1]);
+		if (rc)
+			return rc;
+		if (k > 0) {
+			rc = finish(strips[mine[k - 1]], ctx->buf[(k - 1) & 1]);
+			if (rc)
+				return rc;
+		}
+	}
+	if (!mine.empty()) {
+		int rc = finish(strips[mine.back()], ctx->buf[(mine.size() - 1) & 1]);
+		if (rc)
+			return rc;
+	}
+	// exact cell count of this shard: sum over its strips of sum_{hi} len_hi * (sum_{lo<hi} len_lo)
+	{
+		std::vector<int32_t> len_orig(num);
+		for (int s = 0; s < num; s++)
+			len_orig[ctx->slot_orig[s]] = ctx->slot_len[s];
+		std::vector<int64_t> pre(num + 1, 0);
+		for (int k = 0; k < num; k++)
+			pre[k + 1] = pre[k] + len_orig[k];
+		int64_t cells = 0;
+		for (int idx : mine)
+			for (int hi = strips[idx].a0; hi < strips[idx].a0 + strips[idx].an; hi++)
+				cells += (int64_t)len_orig[hi] * pre[hi];
+		S.cells = cells;
+	}
+	{ // kernel_ms = length of the union of the kernel intervals (two streams overlap)
+		std::sort(spans.begin(), spans.end());
+		double uni = 0, busy = 0, cur_s = 0, cur_e = -1;
+		for (auto &iv : spans) {
+			busy += iv.second - iv.first;
+			if (cur_e < 0 || iv.first > cur_e) {
+				if (cur_e >= 0)
+					uni += cur_e - cur_s;
+				cur_s = iv.first;
+				cur_e = iv.second;
+			} else {
+				cur_e = std::max<double>(cur_e, iv.second);
+			}
+		}
+		if (cur_e >= 0)
+			uni += cur_e - cur_s;
+		S.kernel_ms = uni;
+		S.busy_ms = busy;
+	}
+	if (!mine.empty()) { // everything above has been synchronised; close the device span
+		float dev = 0.f;
+		CU(cudaEventRecord(ctx->ev_span[1], ctx->copy_stream));
+		CU(cudaEventSynchronize(ctx->ev_span[1]));
+		CU(cudaEventElapsedTime(&dev, ctx->ev_span[0], ctx->ev_span[1]));
+		S.device_ms = dev;
+	}
+	S.total_ms = now_ms() - t0;
+	return SAB_OK;
+}
+
+int sab_align(sab_ctx *ctx, int32_t *matrix, int triangular, sab_progress_fn progress, void *user)
+{
+	return sab_align_shard(ctx, 0, 1, matrix, triangular, progress, user);
+}
+
+int sab_plan_strips(const sab_meta *meta, int32_t num, int32_t panel, int32_t nshards,
+		    int32_t max_strips, int32_t *row0, int32_t *rows, int32_t *owner_out)
+{
+	if (!meta || num < 2 || nshards < 1 || panel < 0 || panel % kPanelQuantum)
+		return SAB_ERR_ARG;
+	panel = auto_panel(num, panel, nshards);
+	const int npanels = (num + panel - 1) / panel;
+	if (npanels > max_strips)
+		return npanels;
+	std::vector<double> cost(npanels);
+	double before = 0;
+	for (int p = 0; p < npanels; p++) {
+		const int a0 = p * panel, an = std::min(panel, num - a0);
+		double lq = 0;
+		for (int k = a0; k < a0 + an; k++)
+			lq += meta[k].len;
+		cost[p] = lq * (before + 0.5 * lq);
+		before += lq;
+		if (row0)
+			row0[p] = a0;
+		if (rows)
+			rows[p] = an;
+	}
+	std::vector<int> owner;
+	lpt_assign(cost, nshards, owner);
+	if (owner_out)
+		for (int p = 0; p < npanels; p++)
+			owner_out[p] = owner[p];
+	return npanels;
+}
+
+int sab_strip_count(const sab_ctx *ctx)
+{
+	if (!ctx || !ctx->uploaded)
+		return SAB_ERR_STATE;
+	return (ctx->num + ctx->panel - 1) / ctx->panel;
+}
+
+int sab_strip_info(const sab_ctx *ctx, int32_t strip, int32_t nshards, int32_t *row0, int32_t *rows,
+		   int32_t *owner_out)
+{
+	if (!ctx || !ctx->uploaded)
+		return SAB_ERR_STATE;
+	if (nshards < 1 || strip < 0 || strip >= sab_strip_count(ctx))
+		return SAB_ERR_ARG;
+	std::vector<Strip> strips;
+	std::vector<int> owner;
+	plan_strips(ctx, nshards, strips, owner);
+	if (row0)
+		*row0 = strips[strip].a0;
+	if (rows)
+		*rows = strips[strip].an;
+	if (owner_out)
+		*owner_out = owner[strip];
+	return SAB_OK;
+}
+
+int sab_get_stats(const sab_ctx *ctx, sab_stats *out)
+{
+	if (!ctx || !out)
+		return SAB_ERR_ARG;
+	*out = ctx->stats;
+	return SAB_OK;
+}
+
+} // extern "C"

@@ -54,15 +54,18 @@ struct DeviceSeqs {
 	const uint32_t *rowpack; // [(grp_off[g] + r/4) * 32 + lane] = 4 letters * 4 (byte offsets)
 };
 
+// One launch = one ROW STRIP of the score matrix: the queries are the slots of panel
+// `a` (original indices [a_orig0, a_orig0 + a_n)), the subjects every slot below them.
+// Scores land in the strip buffer in the reference's packed-triangular row layout
+// (src/io/output.c:79-83): blk[tri(hi) - tri(a_orig0) + lo], tri(j) = j(j-1)/2, hi > lo
+// original indices -- so the strip is one contiguous run of the final matrix.
 struct TileParams {
 	DeviceSeqs seqs;
-	int a_slot0, a_n; // query panel   : slots [a_slot0, a_slot0 + a_n)
-	int b_slot0, b_n; // subject panel : slots [b_slot0, b_slot0 + b_n), b_slot0 <= a_slot0
-	int a_orig0, b_orig0; // first original index of each panel
-	int32_t *blk; // blk[(hi - a_orig0) * ld + (lo - b_orig0)], hi > lo original indices
-	int64_t ld;
-	int32_t *blkT; // optional mirror: blkT[(lo - b_orig0) * ldT + (hi - a_orig0)]
-	int64_t ldT;
+	int a_slot0, a_n; // query slots [a_slot0, a_slot0 + a_n); subjects: slots [0, a_slot0 + a_n)
+	int a_orig0; // first original index of the strip (== a_slot0: panels are index ranges)
+	int32_t *blk; // strip buffer, packed-triangular rows
+	int64_t tri0; // tri(a_orig0)
+	int32_t *blkT; // optional mirror for the full layout: blkT[lo * a_n + (hi - a_orig0)]
 	int nqb, nsc, chunk; // work items = nqb query blocks x nsc subject chunks of `chunk` slots
 	unsigned *counter; // dynamic work counter of this launch
 	uint2 *bnd; // strip boundary buffers
@@ -363,8 +366,9 @@ __global__ void __launch_bounds__(kThreads) sab_tile_kernel(const TileParams p)
 		const int t0 = p.a_slot0 + qb * kThreads;
 		const int t = t0 + tid; // my query slot
 		const bool valid = t < a_end;
-		int s_begin = p.b_slot0 + sc * p.chunk;
-		int s_end = min(s_begin + p.chunk, p.b_slot0 + p.b_n);
+		int s_begin = sc * p.chunk;
+		int s_end = s_begin + p.chunk;
+		s_end = min(s_end, a_end);
 		s_end = min(s_end, min(t0 + kThreads, a_end) - 1); // only subjects below the top query
 		if (s_begin >= s_end)
 			continue;
@@ -433,10 +437,9 @@ __global__ void __launch_bounds__(kThreads) sab_tile_kernel(const TileParams p)
 						const int score = h ? sc1 : sc0;
 						const int sorig = p.seqs.slot_orig[ss];
 						const int hi = max(qorig, sorig), lo = min(qorig, sorig);
-						p.blk[(int64_t)(hi - p.a_orig0) * p.ld + (lo - p.b_orig0)] = score;
+						p.blk[(int64_t)hi * (hi - 1) / 2 - p.tri0 + lo] = score;
 						if (p.blkT)
-							p.blkT[(int64_t)(lo - p.b_orig0) * p.ldT + (hi - p.a_orig0)] =
-								score;
+							p.blkT[(int64_t)lo * p.a_n + (hi - p.a_orig0)] = score;
 						if (METHOD == M_SW && PACKED && score > p.ovf_threshold) {
 							const unsigned k = atomicAdd(p.rerun_count, 1u);
 							if (k < p.rerun_cap)
@@ -469,11 +472,10 @@ struct RerunParams {
 	int scratch_cols;
 	const int32_t *sub25; // as TileParams (offset by -gapA)
 	int gapA, gapE;
-	int a_orig0, b_orig0;
+	int a_orig0, a_n;
 	int32_t *blk;
-	int64_t ld;
+	int64_t tri0;
 	int32_t *blkT;
-	int64_t ldT;
 };
 
 __global__ void sab_rerun_sw_kernel(const RerunParams p)
@@ -516,9 +518,9 @@ __global__ void sab_rerun_sw_kernel(const RerunParams p)
 		}
 		const int qo = p.seqs.slot_orig[t], so = p.seqs.slot_orig[s];
 		const int hi = max(qo, so), lo = min(qo, so);
-		p.blk[(int64_t)(hi - p.a_orig0) * p.ld + (lo - p.b_orig0)] = best;
+		p.blk[(int64_t)hi * (hi - 1) / 2 - p.tri0 + lo] = best;
 		if (p.blkT)
-			p.blkT[(int64_t)(lo - p.b_orig0) * p.ldT + (hi - p.a_orig0)] = best;
+			p.blkT[(int64_t)lo * p.a_n + (hi - p.a_orig0)] = best;
 	}
 }
 

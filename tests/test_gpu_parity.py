@@ -1,0 +1,217 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI
+(include/seqalign_b200.h via ctypes), against
+  * the committed golden fixtures (outputs of the unmodified reference CPU build),
+  * the CPU oracle on the same seeded inputs,
+  * size-independent properties at larger sizes.
+Bit-exact: these are int32 scores and filter decisions."""
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, cli_to_config, golden_cases, load_golden, parse_fasta_bytes
+from sequencealigner_b200 import AlignConfig, Aligner, SeqStore, align_all, capi, synth
+
+pytestmark = pytest.mark.gpu
+
+METHODS = [("nw", dict(gap_pen=4)), ("ga", dict(gap_open=10, gap_ext=1)),
+           ("sw", dict(gap_open=10, gap_ext=1))]
+
+
+def gpu_scores(cfg, store, triangular=True, **kw):
+    with Aligner(cfg, **kw) as al:
+        al.upload(store)
+        out = al.align(triangular=triangular)
+        return out, al.stats()
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_golden(name):
+    g = load_golden(name)
+    cfg = cli_to_config(g["args"])
+    mat, kept = align_all(SeqStore.from_sequences(g["seqs"]), cfg, triangular=g["triangular"])
+    assert [kept.sequence(k) for k in range(kept.num)] == g["kept"]
+    assert np.array_equal(mat, g["matrix"])
+
+
+@pytest.mark.parametrize("flags", [0, capi.SAB_FLAG_FORCE_INT32])
+def test_golden_all_tables(flags):
+    z = np.load(GOLDEN / "all_tables.npz")
+    stores = {k: SeqStore.from_sequences(parse_fasta_bytes(z[k])) for k in ("protein", "nucleo")}
+    for key in z.files:
+        if "/" not in key:
+            continue
+        name, method = key.split("/")
+        cfg = AlignConfig(method=method, matrix=name, gap_pen=3) if method == "nw" else \
+            AlignConfig(method=method, matrix=name, gap_open=9, gap_ext=2)
+        store = stores["nucleo" if name in ("dnafull", "nuc44") else "protein"]
+        mat, _ = gpu_scores(cfg, store, triangular=False, flags=flags)
+        assert np.array_equal(mat, z[key]), key
+
+
+@pytest.mark.parametrize("method,kw", METHODS)
+@pytest.mark.parametrize("flags", [0, capi.SAB_FLAG_FORCE_INT32])
+def test_vs_oracle_mixed_lengths(oracle_mod, method, kw, flags):
+    """ragged lengths 1..420 across several panels, strips and register windows"""
+    rng = np.random.default_rng(5)
+    lens = np.concatenate([rng.integers(1, 420, size=560), [1, 1, 2, 31, 32, 33, 127, 128, 129,
+                                                              255, 256, 257, 384, 385, 419]])
+    rng.shuffle(lens)
+    store = SeqStore.from_codes(rng.integers(0, 20, size=int(lens.sum())), lens, synth.PROTEIN20)
+    cfg = AlignConfig(method, "blosum62", **kw)
+    want, _ = oracle_mod.align_all(cfg.resolve(), store, triangular=True)
+    got, st = gpu_scores(cfg, store, triangular=True, panel=256, flags=flags)
+    assert st["pairs"] == store.pairs() and st["cells"] == store.cells()
+    assert (st["tiles_int32"] > 0) == bool(flags)
+    bad = np.flatnonzero(got != want)
+    assert bad.size == 0, (bad[:10], got[bad[:10]], want[bad[:10]])
+
+
+@pytest.mark.parametrize("config", ["c1", "c2", "c3", "c4"])
+def test_vs_oracle_baseline_configs_scaled(oracle_mod, config):
+    """BASELINE.json configs at a size the oracle finishes in seconds"""
+    n = {"c1": 700, "c2": 300, "c3": 500, "c4": 900}[config]
+    store, c = synth.make(config, n=n)
+    cfg = AlignConfig(c["method"], c["matrix"], gap_pen=c.get("gap_pen"),
+                      gap_open=c.get("gap_open"), gap_ext=c.get("gap_ext"))
+    for tri in (True, False):
+        want, _ = oracle_mod.align_all(cfg.resolve(), store, triangular=tri)
+        got, _ = gpu_scores(cfg, store, triangular=tri)
+        assert np.array_equal(got, want)
+
+
+def test_full_layout_matches_triangular_and_diagonal_untouched():
+    store, c = synth.make("c1", n=1000)
+    cfg = AlignConfig("ga", "blosum62", gap_open=10, gap_ext=1)
+    with Aligner(cfg, panel=256) as al:
+        al.upload(store)
+        tri = al.align(triangular=True)
+        full = np.full((store.num, store.num), 7, dtype=np.int32)
+        al.align(triangular=False, out=full)
+    assert (np.diag(full) == 7).all()  # output_fill never writes the diagonal (output.c:76-83)
+    assert (np.tril(full, -1) == np.triu(full, 1).T).all()
+    iu = np.tril_indices(store.num, -1)
+    assert np.array_equal(full[iu], tri)  # tril order is (j, i<j) row-major == packed layout
+
+
+def test_no_write_mode_and_stats():
+    store, _ = synth.make("c3", n=600)
+    cfg = AlignConfig("sw", "nuc44", gap_open=10, gap_ext=1)
+    with Aligner(cfg) as al:
+        al.upload(store)
+        assert al.align(write=False) is None  # -W / --no-write
+        st = al.stats()
+    assert st["pairs"] == store.pairs() and st["cells"] == store.cells()
+    assert st["d2h_bytes"] == 0 and st["kernel_ms"] > 0 and st["launches"] >= 1
+
+
+def test_sw_int16_overflow_rerun(oracle_mod):
+    """C5-ovf: poly-W under pam500 exceeds int16 -> a-posteriori int32 re-run list"""
+    store, c = synth.make_overflow(n=300, planted=6)
+    cfg = AlignConfig("sw", "pam500", gap_open=10, gap_ext=1)
+    want, _ = oracle_mod.align_all(cfg.resolve(), store)
+    assert want.max() == 34000
+    got, st = gpu_scores(cfg, store, flags=capi.SAB_FLAG_FORCE_INT16)
+    assert st["rerun_pairs"] >= 15
+    assert np.array_equal(got, want)
+    got, st = gpu_scores(cfg, store)  # default routing
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("method,kw", [("nw", dict(gap_pen=40)), ("ga", dict(gap_open=60, gap_ext=25))])
+def test_global_methods_route_wide_ranges_to_int32(oracle_mod, method, kw):
+    store, _ = synth.make_overflow(n=200, planted=3)
+    cfg = AlignConfig(method, "pam500", **kw)
+    want, _ = oracle_mod.align_all(cfg.resolve(), store)
+    assert want.min() < -32768 or want.max() > 32767
+    got, st = gpu_scores(cfg, store)
+    assert st["tiles_int32"] == st["tiles"]
+    assert np.array_equal(got, want)
+
+
+def test_two_sequences_and_tiny_sets(oracle_mod):
+    for seqs in (["A", "W"], ["ACDEFGHIKLMNPQRSTVWY", "W"], ["M" * 700, "MK" * 300, "K"]):
+        store = SeqStore.from_sequences(seqs)
+        for method, kw in METHODS:
+            cfg = AlignConfig(method, "blosum62", **kw)
+            want, _ = oracle_mod.align_all(cfg.resolve(), store)
+            got, _ = gpu_scores(cfg, store)
+            assert np.array_equal(got, want), (seqs, method)
+
+
+def test_errors():
+    cfg = AlignConfig("nw", "blosum62", gap_pen=4)
+    with Aligner(cfg) as al:
+        with pytest.raises(capi.SabError):
+            al.align()  # before upload
+        with pytest.raises(capi.SabError):
+            al.upload(SeqStore.from_sequences(["ACD"]))  # SEQ_N_MIN = 2
+        with pytest.raises(capi.SabError):
+            al.upload(SeqStore.from_sequences(["ACD", "AJC"]))  # J is not in the alphabet
+    r = cfg.resolve()
+    r["sub_mat"] = r["sub_mat"].copy()
+    r["sub_mat"][0, 1] += 1
+    with pytest.raises(capi.SabError):
+        Aligner(r)  # asymmetric table
+    with pytest.raises(capi.SabError):
+        Aligner(cfg, device=99)
+
+
+def test_panel_size_and_sharding_do_not_change_results():
+    """idempotence: any panel height / any shard split gives the same matrix"""
+    store, c = synth.make("c5", n=1500)
+    cfg = AlignConfig("sw", "blosum62", gap_open=10, gap_ext=1)
+    base, _ = gpu_scores(cfg, store, panel=128)
+    for panel in (256, 512, 0):
+        got, _ = gpu_scores(cfg, store, panel=panel)
+        assert np.array_equal(got, base)
+    merged = np.full_like(base, -1)
+    with Aligner(cfg, panel=128, shards_hint=3) as al:
+        al.upload(store)
+        owners = al.strips(3)
+        for shard in range(3):
+            part = np.full_like(base, -1)
+            al.align(out=part, shard=shard, nshards=3)
+            for row0, rows, owner in owners:
+                lo, hi = row0 * (row0 - 1) // 2, (row0 + rows) * (row0 + rows - 1) // 2
+                if owner == shard:
+                    merged[lo:hi] = part[lo:hi]
+                else:
+                    assert (part[lo:hi] == -1).all()  # other shards' rows untouched
+    assert np.array_equal(merged, base)
+
+
+@pytest.mark.parametrize("thr", [0.9, 0.5, 0.05, 1.0])
+def test_filter_decisions(oracle_mod, thr):
+    store, c = synth.make("c4", n=5000)
+    want = oracle_mod.filter_lost(store, thr)
+    with Aligner(AlignConfig("ga", "blosum62", gap_open=10, gap_ext=1)) as al:
+        got = al.filter(store, thr)
+    assert want.sum() > 0 and np.array_equal(got, want)
+
+
+def test_filter_ragged_lengths(oracle_mod):
+    rng = np.random.default_rng(3)
+    base = [bytes(rng.choice(list(b"ACDEFGHIK"), size=int(rng.integers(1, 90)))) for _ in range(40)]
+    seqs = []
+    for k in range(3000):
+        s = bytearray(base[int(rng.integers(0, 40))])
+        cut = int(rng.integers(1, len(s) + 1))
+        s = s[:cut] + bytes(rng.choice(list(b"ACDEFGHIK"), size=int(rng.integers(0, 20))))
+        seqs.append(bytes(s))
+    store = SeqStore.from_sequences(seqs)
+    with Aligner(AlignConfig("nw", "blosum62", gap_pen=4)) as al:
+        for thr in (0.8, 0.3):
+            assert np.array_equal(al.filter(store, thr), oracle_mod.filter_lost(store, thr))
+
+
+def test_full_size_properties_c2_slice():
+    """size-independent checks at a size the oracle cannot do in seconds: NW self-consistency
+    (score(i,j) <= min over diagonal sums), SW >= 0 and SW >= NW-free bound, checksums stable"""
+    store, c = synth.make("c2", n=3000)
+    sw, _ = gpu_scores(AlignConfig("sw", "blosum62", gap_open=10, gap_ext=1), store)
+    ga, _ = gpu_scores(AlignConfig("ga", "blosum62", gap_open=10, gap_ext=1), store)
+    nw, _ = gpu_scores(AlignConfig("nw", "blosum62", gap_pen=10), store)
+    assert (sw >= 0).all() and (sw >= ga).all()  # local >= global with the same gaps
+    assert (ga >= nw).all()  # affine(open 10, ext 1) never costs more than linear 10
+    again, _ = gpu_scores(AlignConfig("ga", "blosum62", gap_open=10, gap_ext=1), store, panel=384)
+    assert int(again.astype(np.int64).sum()) == int(ga.astype(np.int64).sum())
+    assert np.array_equal(again, ga)

@@ -1,0 +1,125 @@
+"""CPU-only: host logic and the C-ABI surface (no compute calls without a GPU)."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from sequencealigner_b200 import AlignConfig, SeqStore, capi, matrix_lookup, matrix_names, synth
+from sequencealigner_b200.aligner import plan_strips
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = (ROOT / "include" / "seqalign_b200.h").read_text()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(sab_[a-z0-9_]+)\s*\(", hdr)) - {"sab_progress_fn"}
+    lib = C.CDLL(str(capi.LIB))
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
+    assert capi.load().sab_abi_version() == 1
+
+
+def test_struct_sizes_match_header():
+    assert C.sizeof(capi.SabMeta) == 8
+    assert C.sizeof(capi.SabConfig) == 4 * (4 + 128 + 576 + 4 + 4)
+    assert C.sizeof(capi.SabStats) == 8 * 16
+
+
+def test_no_cpu_fallback_without_device():
+    lib = capi.load()
+    if lib.sab_device_count() > 0:
+        pytest.skip("a device is present")
+    from sequencealigner_b200 import Aligner
+    with pytest.raises(capi.SabError) as e:
+        Aligner(AlignConfig("nw", "blosum62", gap_pen=4))
+    assert e.value.code == -2  # SAB_ERR_NODEVICE
+
+
+def test_matrix_tables():
+    names = matrix_names()
+    assert len(names) == 67 and "blosum62" in names and "nuc44" in names
+    lut, sub = matrix_lookup("BLOSUM62")  # case-insensitive, matrices.c:47
+    order = "ARNDCQEGHILKMFPSTWYVBZX*"
+    assert [lut[ord(c)] for c in order] == list(range(24))
+    assert lut[ord("a")] == -1 and lut[ord("J")] == -1
+    assert sub[lut[ord("W")], lut[ord("W")]] == 11 and sub[lut[ord("A")], lut[ord("R")]] == -1
+    assert (sub == sub.T).all()
+    lut, sub = matrix_lookup("nuc44")
+    assert [lut[ord(c)] for c in "ATGCSWRYKMBVHDN*"] == list(range(16))
+    assert (sub[16:, :] == 0).all()
+    with pytest.raises(ValueError):
+        matrix_lookup("blosum63")
+    for n in names:
+        _, s = matrix_lookup(n)
+        assert (s == s.T).all() and -23 <= s.min() and s.max() <= 35
+
+
+def test_align_config_rules():
+    r = AlignConfig("Gotoh", "blosum62", gap_open=10, gap_ext=1).resolve()
+    assert r["method"] == capi.SAB_GA and r["gap_open"] == -10 and r["gap_ext"] == -1
+    r = AlignConfig("ga", "blosum62", gap_open=4, gap_ext=4).resolve()  # validate_ga, ga.c:70-88
+    assert r["method"] == capi.SAB_NW and r["gap_pen"] == -4
+    with pytest.raises(ValueError):
+        AlignConfig("sw", "blosum62", gap_pen=4).resolve()
+    with pytest.raises(ValueError):
+        AlignConfig("nw", "blosum62", gap_open=4, gap_ext=1).resolve()
+    with pytest.raises(ValueError):
+        AlignConfig("nw", "blosum62").resolve()
+    with pytest.raises(ValueError):
+        AlignConfig("xx", "blosum62", gap_pen=1).resolve()
+    with pytest.raises(ValueError):
+        AlignConfig("nw", "blosum62", gap_pen=1, filter=1.5).resolve()
+
+
+def test_seqstore_layout_and_counts(tmp_path):
+    s = SeqStore.from_sequences(["ACD", "W", "KLMNP"])
+    assert s.seqs.tobytes() == b"ACD\0W\0KLMNP\0"
+    assert s.meta["off"].tolist() == [0, 4, 6] and s.meta["len"].tolist() == [3, 1, 5]
+    assert s.max == 5 and s.pairs() == 3 and s.cells() == 3 * 1 + 3 * 5 + 1 * 5
+    with pytest.raises(ValueError):
+        SeqStore.from_sequences(["AC", ""])
+    p = tmp_path / "a.fasta"
+    p.write_bytes(b">x\nac d\nEF\r\n>y\nWW\n")
+    from sequencealigner_b200 import read_fasta
+    lut, _ = matrix_lookup("blosum62")
+    r = read_fasta(p, lut)
+    assert [r.sequence(k) for k in range(2)] == [b"ACDEF", b"WW"]
+    p.write_bytes(b">x\nAJ\n")
+    with pytest.raises(ValueError):
+        read_fasta(p, lut)
+    store, _ = synth.make("c2", n=50)
+    again = SeqStore.from_sequences([store.sequence(k) for k in range(50)])
+    assert np.array_equal(store.seqs, again.seqs) and np.array_equal(store.meta, again.meta)
+    assert store.head(10).num == 10 and store.head(10).sequence(9) == store.sequence(9)
+
+
+def test_synth_configs_are_deterministic():
+    a, cfg = synth.make("c3", n=64)
+    b, _ = synth.make("c3", n=64)
+    assert np.array_equal(a.seqs, b.seqs) and set(a.seqs.tobytes()) <= set(b"ACGT\0")
+    assert (a.lengths == 150).all() and cfg["method"] == "sw"
+    d, cfg = synth.make("c4", n=400)
+    assert 30 <= d.lengths.min() and d.lengths.max() <= 60 and cfg["filter"] == 0.9
+    o, _ = synth.make_overflow(n=100, planted=4)
+    assert sum(o.sequence(k) == b"W" * 1000 for k in range(100)) == 4
+
+
+def test_strip_plan_covers_rows_once_and_balances():
+    store, _ = synth.make("c5", n=20000)
+    for nshards in (1, 2, 8):
+        plan = plan_strips(store, nshards)
+        rows = sorted((a, a + b) for a, b, _ in plan)
+        assert rows[0][0] == 0 and rows[-1][1] == store.num
+        assert all(rows[k][1] == rows[k + 1][0] for k in range(len(rows) - 1))
+        assert all(b % 128 == 0 for _, b, _ in plan[:-1])
+        lens = store.lengths
+        pre = np.concatenate([[0], np.cumsum(lens)])
+        load = np.zeros(nshards)
+        for a, b, o in plan:
+            load[o] += float((lens[a:a + b] * pre[a:a + b]).sum())
+        assert load.min() > 0 and load.max() / load.mean() < 1.08
+    assert plan_strips(store, 4) == plan_strips(store, 4)  # deterministic on every rank

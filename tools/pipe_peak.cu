@@ -1,0 +1,133 @@
+// tools/pipe_peak.cu -- MEASUREMENT INFRASTRUCTURE (bench.py roofline denominator).
+//
+// the path is bound by the SM integer pipes, and
+// MEASURED_PEAKS.json holds no integer figure, so the peak has to be measured on
+// the box.  Each kernel runs ILP independent dependency chains of one instruction
+// kind per thread on every SM and reports warp-lane instructions per second.
+//   0 VIADDMNMX.S16x2  (__viaddmax_s16x2)     1 VIMNMX3.S16x2 (__vimax3_s16x2)
+//   2 packed 16x2 add  (__vadd2)              3 IADD3 (32-bit add)
+//   4 IMAD (mad.lo, fma pipe)                 5 LDS.32 (conflict free)
+//   6 GA cell mix: 2 viaddmax + 1 vimax3 + 2 vadd2        (all on the alu pipe)
+//   7 GA cell mix with the two adds issued as IMAD        (alu + fma pipes)
+//   8 VIADDMNMX.U16x2                          9 VIMNMX3.U16x2
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+namespace {
+constexpr int ILP = 8;
+constexpr int THREADS = 256;
+
+__device__ __forceinline__ uint32_t imad_add(uint32_t a, uint32_t one, uint32_t b)
+{
+	uint32_t d;
+	asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
+	return d;
+}
+
+template <int OP> __global__ void __launch_bounds__(THREADS) peak_kernel(uint32_t *out, int iters,
+									 uint32_t seed, uint32_t one)
+{
+	__shared__ uint32_t sm[THREADS * 4];
+	uint32_t v[ILP], w[ILP];
+	const uint32_t t = threadIdx.x;
+	for (int k = 0; k < ILP; k++) {
+		v[k] = seed * (k + 1) + t;
+		w[k] = seed ^ (k * 77 + t);
+	}
+	for (int k = t; k < THREADS * 4; k += THREADS)
+		sm[k] = (k * 4 + 4) % (THREADS * 16); // pointer-chase table, byte offsets
+	__syncthreads();
+	const uint32_t c1 = seed | 0x00010001u, c2 = seed & 0x7fff7fffu;
+	for (int it = 0; it < iters; it++) {
+#pragma unroll
+		for (int rep = 0; rep < 4; rep++) {
+#pragma unroll
+			for (int k = 0; k < ILP; k++) {
+				if (OP == 0)
+					v[k] = __viaddmax_s16x2(v[k], c1, c2);
+				else if (OP == 1)
+					v[k] = __vimax3_s16x2(v[k], c1, w[k]);
+				else if (OP == 2)
+					v[k] = __vadd2(v[k], c1);
+				else if (OP == 3)
+					asm volatile("add.u32 %0, %0, %1;" : "+r"(v[k]) : "r"(w[k]));
+				else if (OP == 4)
+					v[k] = imad_add(v[k], one, c1);
+				else if (OP == 5)
+					v[k] = *(const uint32_t *)((const char *)sm + ((v[k] + t * 4) & (THREADS * 16 - 4)));
+				else if (OP == 6) {
+					uint32_t y = __viaddmax_s16x2(w[k], c1, v[k]);
+					uint32_t x = __viaddmax_s16x2(v[k], c1, w[k]);
+					uint32_t d = __vadd2(v[k], c2);
+					uint32_t m = __vimax3_s16x2(d, x, y);
+					v[k] = __vadd2(m, c1);
+					w[k] = y;
+				} else if (OP == 7) {
+					uint32_t y = __viaddmax_u16x2(w[k], c1, v[k]);
+					uint32_t x = __viaddmax_u16x2(v[k], c1, w[k]);
+					uint32_t d = imad_add(v[k], one, c2);
+					uint32_t m = __vimax3_u16x2(d, x, y);
+					v[k] = imad_add(m, one, c1);
+					w[k] = y;
+				} else if (OP == 8)
+					v[k] = __viaddmax_u16x2(v[k], c1, c2);
+				else if (OP == 9)
+					v[k] = __vimax3_u16x2(v[k], c1, w[k]);
+			}
+		}
+	}
+	uint32_t acc = 0;
+	for (int k = 0; k < ILP; k++)
+		acc ^= v[k] ^ w[k];
+	out[blockIdx.x * THREADS + t] = acc;
+}
+
+typedef void (*kfn)(uint32_t *, int, uint32_t, uint32_t);
+kfn KERNELS[] = { peak_kernel<0>, peak_kernel<1>, peak_kernel<2>, peak_kernel<3>, peak_kernel<4>,
+		  peak_kernel<5>, peak_kernel<6>, peak_kernel<7>, peak_kernel<8>, peak_kernel<9> };
+const int INSTR_PER_STEP[] = { 1, 1, 1, 1, 1, 1, 5, 5, 1, 1 };
+} // namespace
+
+// Returns 0 and the measured giga lane-instructions per second of kind `op` on `device`
+// (all SMs busy, best of 5 timed launches), or a negative value on error.
+extern "C" int sab_pipe_peak(int op, int device, double *ginstr_per_s, double *ms_out)
+{
+	if (op < 0 || op > 9 || !ginstr_per_s)
+		return -1;
+	if (cudaSetDevice(device) != cudaSuccess)
+		return -2;
+	cudaDeviceProp prop;
+	if (cudaGetDeviceProperties(&prop, device) != cudaSuccess)
+		return -2;
+	const int blocks = prop.multiProcessorCount * 8; // 2048 threads per SM
+	const int iters = 4096;
+	uint32_t *out = nullptr;
+	if (cudaMalloc(&out, sizeof(uint32_t) * blocks * THREADS) != cudaSuccess)
+		return -3;
+	cudaEvent_t e0, e1;
+	cudaEventCreate(&e0);
+	cudaEventCreate(&e1);
+	float best = 1e30f;
+	for (int rep = 0; rep < 7; rep++) {
+		cudaEventRecord(e0);
+		KERNELS[op]<<<blocks, THREADS>>>(out, iters, 12345u + rep, 1u);
+		cudaEventRecord(e1);
+		if (cudaEventSynchronize(e1) != cudaSuccess) {
+			cudaFree(out);
+			return -4;
+		}
+		float ms = 0;
+		cudaEventElapsedTime(&ms, e0, e1);
+		if (rep >= 2 && ms < best)
+			best = ms;
+	}
+	cudaEventDestroy(e0);
+	cudaEventDestroy(e1);
+	cudaFree(out);
+	const double instr = (double)blocks * THREADS * iters * 4.0 * ILP * INSTR_PER_STEP[op];
+	*ginstr_per_s = instr / (best * 1e-3) / 1e9;
+	if (ms_out)
+		*ms_out = best;
+	return 0;
+}
