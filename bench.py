@@ -217,8 +217,10 @@ def measure_pipe_peak(device: int):
     lib.sab_pipe_peak.restype = C.c_int
     lib.sab_pipe_peak.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     names = {0: "viaddmnmx_s16x2", 1: "vimnmx3_s16x2", 2: "viadd_16x2", 3: "iadd3", 4: "imad",
-             5: "lds32", 6: "ga_mix_alu", 7: "ga_mix_alu_fma", 8: "viaddmnmx_u16x2",
-             9: "vimnmx3_u16x2"}
+             5: "lds32_random", 6: "ga_mix_alu", 7: "ga_mix_dpx_imad", 8: "viaddmnmx_u16x2",
+             9: "vimnmx3_u16x2", 10: "ga_mix_dpx_iadd3", 11: "dpx_iadd3_1to1",
+             12: "lds32_conflict_free", 13: "ga_cell_dpx_iadd3_lds", 14: "ga_cell_dpx_imad_lds",
+             15: "dpx_imad_1to1"}
     out = {}
     for op, name in names.items():
         g, ms = C.c_double(), C.c_double()

@@ -794,6 +794,7 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		p.sub25 = ctx->d_sub25;
 		p.gapA = ctx->gapA;
 		p.gapE = ctx->gapE;
+		p.one = 1u;
 		// SW a-posteriori test: while every M <= 32767 - max(S) the next diagonal step
 		// cannot wrap, so a wrapped pair always shows a running maximum above it first.
 		p.ovf_threshold = 32767 - std::max(ctx->max_s, 0);

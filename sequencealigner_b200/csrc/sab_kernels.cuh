@@ -19,8 +19,15 @@
 //    boundary buffer in global memory that stays L2 resident.
 //  * Five integer instructions per packed cell pair for Gotoh/SW, three for NW:
 //        Y  = viaddmax(Y, ext, Mo_up)         X = viaddmax(X, ext, Mo_left)
-//        d  = vadd(Mo_diag, s - open)         M = vimax3[_relu](d, X, Y)
-//        Mo = vadd(M, open)                   (+ 1/2 vimax3 per cell for SW's running max)
+//        d  = Mo_diag + (s - open)            M = vimax3(d, X, Y)
+//        Mo = M + open                        (+ 1/2 vimax3 per cell for SW's running max)
+//    Measured on B200 (tools/pipe_peak.cu): the DPX ops, IADD3 and the packed VIADD.16x2
+//    all issue on the 16-lane alu pipe, IMAD on the equally wide fma pipe.  The int16
+//    lanes are therefore kept BIASED (value + 0x8000, unsigned): a plain 32-bit add of
+//    an arithmetic-encoded delta (d1 * 65536 + d0) then updates both lanes without any
+//    carry between them as long as the low lane stays inside [0, 65535], which the range
+//    test guarantees.  The two plain adds go to the fma pipe as IMAD (x * 1 + y with the
+//    1 in a uniform register), leaving three DPX ops per packed cell on the alu pipe.
 //  * int16 range: decided a priori per panel tile for the global methods; SW detects
 //    overflow a posteriori from its own running maximum and queues the pair for the
 //    int32 re-run kernel.  The int32 instantiation of the same kernel (one subject per
@@ -74,6 +81,7 @@ struct TileParams {
 	const int32_t *sub25; // [25*25] S[a][q] - gapA, pad row/col = -gapA
 	int gapA; // NW: gap penalty, GA/SW: gap open (<= 0)
 	int gapE; // GA/SW: gap extend (<= 0)
+	uint32_t one; // == 1, kept opaque so the packed adds issue as IMAD on the fma pipe
 	int ovf_threshold; // SW int16: a score above this may have wrapped -> re-run
 	unsigned long long *rerun_list; // (query slot << 32 | subject slot)
 	unsigned *rerun_count;
@@ -83,34 +91,58 @@ struct TileParams {
 // ---------------------------------------------------------------------------------------
 // Vector ops: two int16 lanes per register (Blackwell DPX) or one int32.
 // ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t imad_add(uint32_t a, uint32_t one, uint32_t b)
+{
+	uint32_t d; // a * 1 + b on the fma pipe; `one` lives in a uniform register
+	asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
+	return d;
+}
+
 template <bool PACKED> struct VOps;
 
+// Two biased int16 lanes (stored value = score + 0x8000, compared unsigned).
 template <> struct VOps<true> {
-	static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) { return __vadd2(a, b); }
+	static constexpr int kBias = 0x8000;
+	// both lanes += the same / a per-lane signed delta, as ONE 32-bit add
+	static __device__ __forceinline__ uint32_t delta(int v) { return (uint32_t)(v * 0x10001); }
+	static __device__ __forceinline__ uint32_t delta2(int lo, int hi)
+	{
+		return (uint32_t)(hi * 65536 + lo);
+	}
+	static __device__ __forceinline__ uint32_t addw(uint32_t a, uint32_t d, uint32_t one)
+	{
+		return imad_add(a, one, d);
+	}
+	// per-lane addend for the DPX add-max ops (wraps inside each lane)
+	static __device__ __forceinline__ uint32_t lane(int v)
+	{
+		return ((uint32_t)v & 0xffffu) * 0x10001u;
+	}
 	static __device__ __forceinline__ uint32_t addmax(uint32_t a, uint32_t b, uint32_t c)
 	{
-		return __viaddmax_s16x2(a, b, c);
+		return __viaddmax_u16x2(a, b, c);
 	}
 	static __device__ __forceinline__ uint32_t max3(uint32_t a, uint32_t b, uint32_t c)
 	{
-		return __vimax3_s16x2(a, b, c);
+		return __vimax3_u16x2(a, b, c);
 	}
-	static __device__ __forceinline__ uint32_t max3_relu(uint32_t a, uint32_t b, uint32_t c)
-	{
-		return __vimax3_s16x2_relu(a, b, c);
-	}
-	static __device__ __forceinline__ uint32_t bcast(int v)
-	{
-		uint32_t u = (uint32_t)v & 0xffffu;
-		return u | (u << 16);
-	}
-	// -inf stand-in: NEG + ext == -32768 exactly, so the first use can never wrap and
+	static __device__ __forceinline__ uint32_t bcast(int v) { return lane(v + kBias); }
+	// -inf stand-in: NEG + ext == biased 0 exactly, so the first use can never wrap and
 	// always loses the max against a real (range-checked) value.
-	static __device__ __forceinline__ uint32_t neg_inf(int ext) { return bcast(-32768 - ext); }
+	static __device__ __forceinline__ uint32_t neg_inf(int ext) { return lane(-ext); }
+	static __device__ __forceinline__ int lo(uint32_t v) { return (int)(v & 0xffffu) - kBias; }
+	static __device__ __forceinline__ int hi(uint32_t v) { return (int)(v >> 16) - kBias; }
 };
 
+// One int32 lane, the reference's own arithmetic (SCORE_MIN sentinel, src/bio/align.h:19).
 template <> struct VOps<false> {
-	static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) { return a + b; }
+	static __device__ __forceinline__ uint32_t delta(int v) { return (uint32_t)v; }
+	static __device__ __forceinline__ uint32_t delta2(int lo, int) { return (uint32_t)lo; }
+	static __device__ __forceinline__ uint32_t addw(uint32_t a, uint32_t d, uint32_t one)
+	{
+		return imad_add(a, one, d);
+	}
+	static __device__ __forceinline__ uint32_t lane(int v) { return (uint32_t)v; }
 	static __device__ __forceinline__ uint32_t addmax(uint32_t a, uint32_t b, uint32_t c)
 	{
 		return (uint32_t)__viaddmax_s32((int)a, (int)b, (int)c);
@@ -119,13 +151,10 @@ template <> struct VOps<false> {
 	{
 		return (uint32_t)__vimax3_s32((int)a, (int)b, (int)c);
 	}
-	static __device__ __forceinline__ uint32_t max3_relu(uint32_t a, uint32_t b, uint32_t c)
-	{
-		return (uint32_t)__vimax3_s32_relu((int)a, (int)b, (int)c);
-	}
 	static __device__ __forceinline__ uint32_t bcast(int v) { return (uint32_t)v; }
-	// SCORE_MIN of the reference (src/bio/align.h:19)
 	static __device__ __forceinline__ uint32_t neg_inf(int) { return (uint32_t)(INT32_MIN / 2); }
+	static __device__ __forceinline__ int lo(uint32_t v) { return (int)v; }
+	static __device__ __forceinline__ int hi(uint32_t) { return 0; }
 };
 
 // ---------------------------------------------------------------------------------------
@@ -139,19 +168,23 @@ template <int METHOD, bool PACKED>
 __device__ __forceinline__ void run_strip(const uint32_t *__restrict__ prof_s,
 					  const uint32_t *__restrict__ rowp, uint2 *__restrict__ bnd,
 					  const int Lq, const int c0, const bool first, const bool last,
-					  const int gA, const int gE, uint32_t &best, uint32_t &res,
-					  const int cap0, const int cap1)
+					  const int gA, const int gE, const uint32_t one, uint32_t &best,
+					  uint32_t &res, const int cap0, const int cap1)
 {
 	using O = VOps<PACKED>;
 	constexpr int K = kStrip;
-	const uint32_t vA = O::bcast(gA);
-	const uint32_t vE = O::bcast(gE);
+	const uint32_t dA = O::delta(gA); // 32-bit-add form of "+ gapA" on every lane
+	const uint32_t lE = O::lane(gE); // per-lane form of "+ gapE" for the DPX add-max
 	const uint32_t NEG = O::neg_inf(gE);
+	const uint32_t ZERO = O::bcast(0); // SW floor
 
 	// Row 0 of the DP (borders): Mo[c] = M[0][C] + gapA with C = c0 + c + 1.
 	//   NW  M[0][C] = C*g               (nw.c:13-14)
 	//   GA  M[0][C] = open + (C-1)*ext  (ga.c:26-30)      Y[0][C] = -inf
 	//   SW  M[0][C] = 0                 (sw.c:21-24)      Y[0][C] = -inf
+	// SW keeps Y floored at 0 (Yf = max(Y, 0)): M = max(0, d, X, Y) = max(d, X, Yf) and
+	// Yf' = max(Yf + ext, Mo_up, 0) is exact for the floored value, so the zero floor costs
+	// no extra alu-pipe instruction.
 	uint32_t Mo[K], Y[K];
 	{
 		int m0, st;
@@ -165,18 +198,18 @@ __device__ __forceinline__ void run_strip(const uint32_t *__restrict__ prof_s,
 			m0 = gA;
 			st = 0;
 		}
-		const uint32_t vst = O::bcast(st);
+		const uint32_t dst = O::delta(st);
 		Mo[0] = O::bcast(m0);
-		Y[0] = NEG;
+		Y[0] = (METHOD == M_SW) ? ZERO : NEG;
 #pragma unroll
 		for (int c = 1; c < K; c++) {
-			Mo[c] = O::add(Mo[c - 1], vst);
-			Y[c] = NEG;
+			Mo[c] = Mo[c - 1] + dst;
+			Y[c] = Y[0];
 		}
 	}
 	// diag for row 1 = M[0][c0] + gapA; left border generator for the first strip:
 	// bl(R) = M[R][0] + gapA, R = 1.. (nw.c:16-17, ga.c:32-38, sw.c:26-30)
-	uint32_t diag, bl, vstep;
+	uint32_t diag, bl, dstep;
 	{
 		int d0, b0, st;
 		if (METHOD == M_NW) {
@@ -194,7 +227,7 @@ __device__ __forceinline__ void run_strip(const uint32_t *__restrict__ prof_s,
 		}
 		diag = O::bcast(d0);
 		bl = O::bcast(b0);
-		vstep = O::bcast(st);
+		dstep = O::delta(st);
 	}
 
 	auto step = [&](const uint32_t qoff, const uint2 bin, const int r) {
@@ -202,7 +235,7 @@ __device__ __forceinline__ void run_strip(const uint32_t *__restrict__ prof_s,
 		if (first) {
 			ml = bl;
 			x = NEG;
-			bl = O::add(bl, vstep);
+			bl += dstep;
 		} else {
 			ml = bin.x;
 			x = bin.y;
@@ -216,14 +249,24 @@ __device__ __forceinline__ void run_strip(const uint32_t *__restrict__ prof_s,
 		for (int c = 0; c < K; c++) {
 			const uint32_t s = pq[c * kProfStride];
 			const uint32_t t = Mo[c];
-			const uint32_t d = O::add(dg, s);
+			const uint32_t d = O::addw(dg, s, one); // fma pipe
 			uint32_t m;
 			if (METHOD == M_NW) {
 				m = O::max3(d, ml, t);
 			} else {
-				const uint32_t y = O::addmax(Y[c], vE, t);
-				x = O::addmax(x, vE, ml);
-				m = (METHOD == M_SW) ? O::max3_relu(d, x, y) : O::max3(d, x, y);
+				uint32_t y;
+				if (METHOD == M_SW) {
+					if (PACKED) {
+						const uint32_t ye = O::addw(Y[c], O::delta(gE), one); // fma pipe
+						y = O::max3(ye, t, ZERO);
+					} else {
+						y = (uint32_t)__viaddmax_s32_relu((int)Y[c], gE, (int)t);
+					}
+				} else {
+					y = O::addmax(Y[c], lE, t);
+				}
+				x = O::addmax(x, lE, ml);
+				m = O::max3(d, x, y);
 				Y[c] = y;
 			}
 			if (METHOD == M_SW) {
@@ -232,7 +275,7 @@ __device__ __forceinline__ void run_strip(const uint32_t *__restrict__ prof_s,
 				else
 					mprev = m;
 			}
-			ml = O::add(m, vA);
+			ml = O::addw(m, dA, one); // fma pipe
 			dg = t;
 			Mo[c] = ml;
 		}
@@ -344,10 +387,7 @@ __global__ void __launch_bounds__(kThreads) sab_tile_kernel(const TileParams p)
 			const int32_t *r1 = ssub + a1 * kLetters;
 #pragma unroll 5
 			for (int q = 0; q < kLetters; q++) {
-				if (PACKED)
-					dst[q] = ((uint32_t)r0[q] & 0xffffu) | ((uint32_t)r1[q] << 16);
-				else
-					dst[q] = (uint32_t)r0[q];
+				dst[q] = VOps<PACKED>::delta2(r0[q], r1[q]);
 			}
 		}
 	};
@@ -390,6 +430,7 @@ __global__ void __launch_bounds__(kThreads) sab_tile_kernel(const TileParams p)
 		build(s, s_end, w, buf);
 		__syncthreads();
 		uint32_t best = 0, res = 0;
+		const uint32_t one = p.one;
 		while (s < s_end) {
 			// next unit
 			int ns = s, nw = w + 1, nLp = Lp;
@@ -407,7 +448,7 @@ __global__ void __launch_bounds__(kThreads) sab_tile_kernel(const TileParams p)
 				const int l0 = p.seqs.slot_len[s];
 				const int l1 = (PACKED && s + 1 < s_end) ? p.seqs.slot_len[s + 1] : 0;
 				if (w == 0) {
-					best = 0;
+					best = VOps<PACKED>::bcast(0);
 					res = 0;
 				}
 				const int cend = min((w + 1) * kWindow, Lp);
@@ -415,20 +456,22 @@ __global__ void __launch_bounds__(kThreads) sab_tile_kernel(const TileParams p)
 				for (int c0 = w * kWindow; c0 < cend; c0 += kStrip) {
 					run_strip<METHOD, PACKED>(pw + (c0 - w * kWindow) * kProfStride, rowp, bnd,
 								  Lq, c0, c0 == 0, c0 + kStrip >= Lp, p.gapA,
-								  p.gapE, best, res, l0 - 1 - c0,
+								  p.gapE, one, best, res, l0 - 1 - c0,
 								  l1 - 1 - c0);
 				}
 				if (cend == Lp) { // pair finished: emit scores
-					int sc0, sc1 = 0;
+					using O = VOps<PACKED>;
+					int sc0, sc1;
 					if (METHOD == M_SW) {
-						sc0 = PACKED ? (int)(int16_t)(best & 0xffffu) : (int)best;
-						if (PACKED)
-							sc1 = (int)(int16_t)(best >> 16);
+						sc0 = O::lo(best);
+						sc1 = O::hi(best);
 					} else {
-						sc0 = (PACKED ? (int)(int16_t)(res & 0xffffu) : (int)res) - p.gapA;
-						if (PACKED)
-							sc1 = (int)(int16_t)(res >> 16) - p.gapA;
+						sc0 = O::lo(res) - p.gapA;
+						sc1 = O::hi(res) - p.gapA;
 					}
+					// a wrapped LOW lane carries into the high lane of the 32-bit adds:
+					// its partner is re-run with it
+					const bool lo_ovf = METHOD == M_SW && PACKED && sc0 > p.ovf_threshold;
 #pragma unroll
 					for (int h = 0; h < NS; h++) {
 						const int ss = s + h;
@@ -440,7 +483,7 @@ __global__ void __launch_bounds__(kThreads) sab_tile_kernel(const TileParams p)
 						p.blk[(int64_t)hi * (hi - 1) / 2 - p.tri0 + lo] = score;
 						if (p.blkT)
 							p.blkT[(int64_t)lo * p.a_n + (hi - p.a_orig0)] = score;
-						if (METHOD == M_SW && PACKED && score > p.ovf_threshold) {
+						if (METHOD == M_SW && PACKED && (score > p.ovf_threshold || lo_ovf)) {
 							const unsigned k = atomicAdd(p.rerun_count, 1u);
 							if (k < p.rerun_cap)
 								p.rerun_list[k] =

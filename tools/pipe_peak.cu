@@ -10,6 +10,10 @@
 //   6 GA cell mix: 2 viaddmax + 1 vimax3 + 2 vadd2        (all on the alu pipe)
 //   7 GA cell mix with the two adds issued as IMAD        (alu + fma pipes)
 //   8 VIADDMNMX.U16x2                          9 VIMNMX3.U16x2
+//  10 GA cell mix with the two adds as IADD3 (add.u32)    11 1 DPX : 1 IADD3
+//  12 LDS.32 conflict free (lane-linear addresses)
+//  13 GA cell as the tile kernel issues it: 3 DPX + 2 IADD3 + 1 LDS
+//  14 same with IMAD adds                      15 1 DPX : 1 IMAD
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -29,14 +33,18 @@ template <int OP> __global__ void __launch_bounds__(THREADS) peak_kernel(uint32_
 									 uint32_t seed, uint32_t one)
 {
 	__shared__ uint32_t sm[THREADS * 4];
+	__shared__ uint32_t sm2[THREADS * 4];
+	const uint32_t zero = one - 1u;
 	uint32_t v[ILP], w[ILP];
 	const uint32_t t = threadIdx.x;
 	for (int k = 0; k < ILP; k++) {
 		v[k] = seed * (k + 1) + t;
 		w[k] = seed ^ (k * 77 + t);
 	}
-	for (int k = t; k < THREADS * 4; k += THREADS)
+	for (int k = t; k < THREADS * 4; k += THREADS) {
 		sm[k] = (k * 4 + 4) % (THREADS * 16); // pointer-chase table, byte offsets
+		sm2[k] = zero;
+	}
 	__syncthreads();
 	const uint32_t c1 = seed | 0x00010001u, c2 = seed & 0x7fff7fffu;
 	for (int it = 0; it < iters; it++) {
@@ -74,6 +82,41 @@ template <int OP> __global__ void __launch_bounds__(THREADS) peak_kernel(uint32_
 					v[k] = __viaddmax_u16x2(v[k], c1, c2);
 				else if (OP == 9)
 					v[k] = __vimax3_u16x2(v[k], c1, w[k]);
+				else if (OP == 10) {
+					uint32_t y = __viaddmax_u16x2(w[k], c1, v[k]);
+					uint32_t x = __viaddmax_u16x2(v[k], c1, w[k]);
+					uint32_t d = v[k];
+					asm volatile("add.u32 %0, %0, %1;" : "+r"(d) : "r"(c2));
+					uint32_t m = __vimax3_u16x2(d, x, y);
+					asm volatile("add.u32 %0, %0, %1;" : "+r"(m) : "r"(c1));
+					v[k] = m;
+					w[k] = y;
+				} else if (OP == 11) {
+					v[k] = __viaddmax_u16x2(v[k], c1, c2);
+					asm volatile("add.u32 %0, %0, %1;" : "+r"(w[k]) : "r"(c1));
+				} else if (OP == 12) {
+					// conflict free: lane-linear word addresses, chain through the value (always 0)
+					v[k] = sm2[(t + k * 32 + v[k]) & (THREADS * 4 - 1)];
+				} else if (OP == 13 || OP == 14) {
+					const uint32_t sc = sm2[(t + k * 32 + (w[k] & zero)) & (THREADS * 4 - 1)];
+					uint32_t y = __viaddmax_u16x2(w[k], c1, v[k]);
+					uint32_t x = __viaddmax_u16x2(v[k], c1, w[k]);
+					uint32_t d = v[k];
+					if (OP == 13)
+						asm volatile("add.u32 %0, %0, %1;" : "+r"(d) : "r"(sc));
+					else
+						d = imad_add(d, one, sc);
+					uint32_t m = __vimax3_u16x2(d, x, y);
+					if (OP == 13)
+						asm volatile("add.u32 %0, %0, %1;" : "+r"(m) : "r"(c1));
+					else
+						m = imad_add(m, one, c1);
+					v[k] = m;
+					w[k] = y;
+				} else if (OP == 15) {
+					v[k] = __viaddmax_u16x2(v[k], c1, c2);
+					w[k] = imad_add(w[k], one, c1);
+				}
 			}
 		}
 	}
@@ -85,15 +128,17 @@ template <int OP> __global__ void __launch_bounds__(THREADS) peak_kernel(uint32_
 
 typedef void (*kfn)(uint32_t *, int, uint32_t, uint32_t);
 kfn KERNELS[] = { peak_kernel<0>, peak_kernel<1>, peak_kernel<2>, peak_kernel<3>, peak_kernel<4>,
-		  peak_kernel<5>, peak_kernel<6>, peak_kernel<7>, peak_kernel<8>, peak_kernel<9> };
-const int INSTR_PER_STEP[] = { 1, 1, 1, 1, 1, 1, 5, 5, 1, 1 };
+		  peak_kernel<5>, peak_kernel<6>, peak_kernel<7>, peak_kernel<8>, peak_kernel<9>,
+		  peak_kernel<10>, peak_kernel<11>, peak_kernel<12>, peak_kernel<13>,
+		  peak_kernel<14>, peak_kernel<15> };
+const int INSTR_PER_STEP[] = { 1, 1, 1, 1, 1, 1, 5, 5, 1, 1, 5, 2, 1, 6, 6, 2 };
 } // namespace
 
 // Returns 0 and the measured giga lane-instructions per second of kind `op` on `device`
 // (all SMs busy, best of 5 timed launches), or a negative value on error.
 extern "C" int sab_pipe_peak(int op, int device, double *ginstr_per_s, double *ms_out)
 {
-	if (op < 0 || op > 9 || !ginstr_per_s)
+	if (op < 0 || op > 15 || !ginstr_per_s)
 		return -1;
 	if (cudaSetDevice(device) != cudaSuccess)
 		return -2;
