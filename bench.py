@@ -253,7 +253,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    al = Aligner(cfg, device=local_rank, shards_hint=n_gpus)
+    al = Aligner(cfg, device=local_rank, shards_hint=n_gpus, flags=args.flags, panel=args.panel)
     al.upload(store)
     n = store.num
     host_matrix = np.zeros(n * (n - 1) // 2, dtype=np.int32)
@@ -381,6 +381,8 @@ def main():
     ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5"])
     ap.add_argument("--n", type=int, default=None, help="override the sequence count")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--flags", type=int, default=0, help="sab_config.flags (tuning / A-B runs)")
+    ap.add_argument("--panel", type=int, default=0, help="sab_config.panel (0 = auto)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     args = ap.parse_args()
     if args.steps < 1:

@@ -15,7 +15,7 @@ CSRC = PKG / "csrc"
 LIB = PKG / "libseqalign_b200.so"
 PIPE_LIB = PKG / "libsab_pipepeak.so"
 SOURCES = ["sab_capi.cu", "sab_filter.cu", "sab_tables.cpp"]
-HEADERS = ["sab_kernels.cuh", "sab_internal.h", "submat_tables.inc", "../../include/seqalign_b200.h"]
+HEADERS = ["sab_kernels.cuh", "sab_wave.cuh", "sab_internal.h", "submat_tables.inc", "../../include/seqalign_b200.h"]
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC,-O3,-Wall,-Wno-unused-function", "-shared", "-cudart", "shared",

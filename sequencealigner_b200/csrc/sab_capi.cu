@@ -12,6 +12,7 @@
 // compute entry point returns SAB_ERR_NODEVICE / SAB_ERR_CUDA.
 #include "sab_internal.h"
 #include "sab_kernels.cuh"
+#include "sab_wave.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -87,7 +88,8 @@ struct sab_ctx {
 	cudaStream_t copy_stream = nullptr;
 	cudaEvent_t ev_copy[2] = { nullptr, nullptr };
 	cudaEvent_t ev_span[2] = { nullptr, nullptr }; // first kernel start / last kernel end
-	int grid_blocks[3][2]{}; // [method][packed] resident persistent blocks
+	int grid_blocks[3][2]{}; // [method][packed] resident persistent blocks (panel kernel)
+	int wave_blocks[3][2]{}; // same for the systolic strip-pipeline kernel
 	sab_stats stats{};
 };
 
@@ -116,6 +118,23 @@ int fail(sab_ctx *c, int code, const char *fmt, ...)
 	} while (0)
 
 typedef void (*tile_kernel_t)(const TileParams);
+
+template <int MINB> tile_kernel_t pick_wave_kernel_t(int method, bool packed)
+{
+	switch (method * 2 + (packed ? 1 : 0)) {
+	case 0: return sab::sab_wave_kernel<sab::M_NW, false, MINB>;
+	case 1: return sab::sab_wave_kernel<sab::M_NW, true, MINB>;
+	case 2: return sab::sab_wave_kernel<sab::M_GA, false, MINB>;
+	case 3: return sab::sab_wave_kernel<sab::M_GA, true, MINB>;
+	case 4: return sab::sab_wave_kernel<sab::M_SW, false, MINB>;
+	default: return sab::sab_wave_kernel<sab::M_SW, true, MINB>;
+	}
+}
+
+tile_kernel_t pick_wave_kernel(int method, bool packed, bool occ4)
+{
+	return occ4 ? pick_wave_kernel_t<4>(method, packed) : pick_wave_kernel_t<3>(method, packed);
+}
 
 tile_kernel_t pick_kernel(int method, bool packed)
 {
@@ -398,6 +417,15 @@ int sab_create(sab_ctx **out, const sab_config *cfg)
 			if (occ < 1)
 				return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
 			ctx->grid_blocks[m][pk] = occ * ctx->sm_count;
+			tile_kernel_t wk = pick_wave_kernel(m, pk, ctx->cfg.flags & SAB_FLAG_WAVE_OCC4);
+			CU(cudaFuncSetAttribute((const void *)wk,
+						cudaFuncAttributeMaxDynamicSharedMemorySize,
+						sab::kWaveSmemBytes));
+			CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+				&occ, (const void *)wk, sab::kWaveThreads, sab::kWaveSmemBytes));
+			if (occ < 1)
+				return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
+			ctx->wave_blocks[m][pk] = occ * ctx->sm_count;
 		}
 	for (int i = 0; i < 2; i++) {
 		StripBuf &b = ctx->buf[i];
@@ -759,7 +787,8 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 
 	auto launch = [&](const Strip &st, StripBuf &b) -> int {
 		const bool packed = st.packed;
-		const int grid = ctx->grid_blocks[method][packed];
+		const bool wave = !(ctx->cfg.flags & SAB_FLAG_PANEL_KERNEL);
+		const int grid = wave ? ctx->wave_blocks[method][packed] : ctx->grid_blocks[method][packed];
 		const int a1 = st.a0 + st.an;
 		const size_t blk_elems = (size_t)(tri(a1) - tri(st.a0));
 		int rc = ensure(ctx, (void **)&b.blk, &b.blk_cap, std::max<size_t>(blk_elems, 1),
@@ -805,7 +834,11 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		if (S.launches == 0)
 			CU(cudaEventRecord(ctx->ev_span[0], b.stream));
 		CU(cudaEventRecord(b.ev_start, b.stream));
-		pick_kernel(method, packed)<<<grid, sab::kThreads, sab::kSmemBytes, b.stream>>>(p);
+		if (wave)
+			pick_wave_kernel(method, packed, ctx->cfg.flags & SAB_FLAG_WAVE_OCC4)<<<grid, sab::kWaveThreads, sab::kWaveSmemBytes,
+							   b.stream>>>(p);
+		else
+			pick_kernel(method, packed)<<<grid, sab::kThreads, sab::kSmemBytes, b.stream>>>(p);
 		CU(cudaGetLastError());
 		CU(cudaEventRecord(b.ev_done, b.stream));
 		S.launches++;
