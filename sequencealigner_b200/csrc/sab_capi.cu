@@ -31,7 +31,7 @@ namespace {
 using sab::DeviceSeqs;
 using sab::TileParams;
 
-constexpr int kPanelQuantum = sab::kThreads; // panels are multiples of the query block
+constexpr int kPanelQuantum = 128; // panels are multiples of 4 query groups
 constexpr size_t kStageBytes = 32u << 20; // pinned bounce buffer (x2)
 constexpr unsigned kRerunCap = 1u << 20;
 constexpr int kRerunThreads = 4096;
@@ -88,8 +88,7 @@ struct sab_ctx {
 	cudaStream_t copy_stream = nullptr;
 	cudaEvent_t ev_copy[2] = { nullptr, nullptr };
 	cudaEvent_t ev_span[2] = { nullptr, nullptr }; // first kernel start / last kernel end
-	int grid_blocks[3][2]{}; // [method][packed] resident persistent blocks (panel kernel)
-	int wave_blocks[3][2]{}; // same for the systolic strip-pipeline kernel
+	int wave_blocks[3][2]{}; // [method][packed] resident persistent blocks of the kernel
 	sab_stats stats{};
 };
 
@@ -134,18 +133,6 @@ template <int MINB> tile_kernel_t pick_wave_kernel_t(int method, bool packed)
 tile_kernel_t pick_wave_kernel(int method, bool packed, bool occ4)
 {
 	return occ4 ? pick_wave_kernel_t<4>(method, packed) : pick_wave_kernel_t<3>(method, packed);
-}
-
-tile_kernel_t pick_kernel(int method, bool packed)
-{
-	switch (method * 2 + (packed ? 1 : 0)) {
-	case 0: return sab::sab_tile_kernel<sab::M_NW, false>;
-	case 1: return sab::sab_tile_kernel<sab::M_NW, true>;
-	case 2: return sab::sab_tile_kernel<sab::M_GA, false>;
-	case 3: return sab::sab_tile_kernel<sab::M_GA, true>;
-	case 4: return sab::sab_tile_kernel<sab::M_SW, false>;
-	default: return sab::sab_tile_kernel<sab::M_SW, true>;
-	}
 }
 
 void free_seqs(sab_ctx *c)
@@ -218,26 +205,46 @@ void copy_segments(const std::vector<Seg> &segs)
 		t.join();
 }
 
-// A-priori int16 range test for a strip.  lq/ls are the
-// longest query / subject of the strip; the DP is swept over subject columns
-// padded to the register-strip width.
-bool int16_safe(const sab_ctx *c, int lq, int ls)
+// Range of everything the kernel stores or forms for a strip whose longest query / subject
+// are lq / ls, in the stored coordinates of sab_wave.cuh.  The DP is
+// swept over subject columns padded to the register-strip width (pad letter scores 0).
+//   NW  V = H - g(r+c):  0 <= V (all-gap path) and H <= min(r,c) max(S)
+//   GA  V = M - e(r+c):  2o <= V, X and Y >= 3o, M <= min(r,c) max(S)
+//   SW  V = M + o, X, Y: -inf stand-ins aside, o + e <= everything <= min(r,c) max(S)
+// plus the transient diagonal sum V + (S - shift) and the (o - e) steps.
+void stored_range(const sab_ctx *c, int lq, int ls, int64_t *low, int64_t *high)
 {
 	const int64_t lsp = ((int64_t)ls + sab::kStrip - 1) / sab::kStrip * sab::kStrip;
 	const int64_t gA = c->gapA, gE = c->gapE;
-	const int64_t hi = (int64_t)std::min<int64_t>(lq, lsp) * std::max(c->max_s, 0);
-	int64_t lo;
+	const int64_t smax = std::max(c->max_s, 0), smin = std::min(c->min_s, 0);
+	const int64_t top = std::min<int64_t>(lq, lsp) * smax;
 	switch (c->cfg.method) {
-	case SAB_NW: lo = (lq + lsp + 2) * gA; break;
-	case SAB_GA: lo = 2 * gA + (lq + lsp) * gE; break;
-	default: lo = 0; break;
+	case SAB_NW:
+		*low = smin + 2 * gA;
+		*high = top - gA * (lq + lsp + 2) + smax;
+		break;
+	case SAB_GA:
+		*low = 3 * gA + 3 * gE + smin;
+		*high = top - gE * (lq + lsp + 2) + smax - gA - gE;
+		break;
+	default:
+		*low = 2 * gA + 2 * gE + smin;
+		*high = top + smax - gA;
+		break;
 	}
-	// stored values: M + gapA, Y >= M + gapA, transient Y + gapE, diag + (S - gapA)
-	const int64_t low = lo + gA + gE + std::min(c->min_s, 0);
-	const int64_t high = (c->cfg.method == SAB_SW ? 0 : hi) + std::max(c->max_s, 0) - gA;
-	// profile entries S - gapA and the SW threshold arithmetic must fit as well
-	if (c->max_s - gA > 16000 || c->min_s - gA < -16000 || -gA > 8000 || -gE > 8000)
+}
+
+bool int16_safe(const sab_ctx *c, int lq, int ls)
+{
+	const int64_t gA = c->gapA, gE = c->gapE;
+	const int64_t shift = sab::profile_shift(c->cfg.method, c->gapA, c->gapE);
+	// profile entries S - shift, the per-lane gap constants and the SW threshold arithmetic
+	if (c->max_s - shift > 16000 || c->min_s - shift < -16000 || -gA > 8000 || -gE > 8000)
 		return false;
+	int64_t low, high;
+	stored_range(c, lq, ls, &low, &high);
+	if (c->cfg.method == SAB_SW)
+		high = std::max<int64_t>(c->max_s, 0) - gA; // wraps are caught a posteriori (re-run)
 	return low >= -32000 && high <= 32000;
 }
 
@@ -273,12 +280,9 @@ void lpt_assign(const std::vector<double> &cost, int nshards, std::vector<int> &
 
 bool int32_safe(const sab_ctx *c, int lq, int ls)
 {
-	const int64_t lsp = (int64_t)ls + sab::kStrip;
-	const int64_t gA = c->gapA, gE = c->gapE;
-	const int64_t hi = (int64_t)std::min<int64_t>(lq, lsp) * std::max(c->max_s, 0) - gA;
-	int64_t lo = (c->cfg.method == SAB_NW) ? (lq + lsp + 2) * gA : 2 * gA + (lq + lsp) * gE;
-	lo += gA + gE + std::min(c->min_s, 0);
-	return hi < (1ll << 29) && lo > -(1ll << 29);
+	int64_t low, high;
+	stored_range(c, lq, ls, &low, &high);
+	return high < (1ll << 29) && low > -(1ll << 29);
 }
 
 } // namespace
@@ -384,7 +388,8 @@ int sab_create(sab_ctx **out, const sab_config *cfg)
 	for (int a = 0; a < sab::kLetters; a++)
 		for (int b = 0; b < sab::kLetters; b++) {
 			const int v = (a < 24 && b < 24) ? cfg->sub_mat[a * 24 + b] : 0;
-			ctx->sub25[a * sab::kLetters + b] = v - ctx->gapA;
+			ctx->sub25[a * sab::kLetters + b] =
+				v - sab::profile_shift(cfg->method, ctx->gapA, ctx->gapE);
 		}
 
 	int ndev = 0;
@@ -407,16 +412,7 @@ int sab_create(sab_ctx **out, const sab_config *cfg)
 	CU(cudaMemcpy(ctx->d_sub25, ctx->sub25, sizeof ctx->sub25, cudaMemcpyHostToDevice));
 	for (int m = 0; m < 3; m++)
 		for (int pk = 0; pk < 2; pk++) {
-			tile_kernel_t k = pick_kernel(m, pk);
-			CU(cudaFuncSetAttribute((const void *)k,
-						cudaFuncAttributeMaxDynamicSharedMemorySize,
-						sab::kSmemBytes));
 			int occ = 0;
-			CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)k,
-									 sab::kThreads, sab::kSmemBytes));
-			if (occ < 1)
-				return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
-			ctx->grid_blocks[m][pk] = occ * ctx->sm_count;
 			tile_kernel_t wk = pick_wave_kernel(m, pk, ctx->cfg.flags & SAB_FLAG_WAVE_OCC4);
 			CU(cudaFuncSetAttribute((const void *)wk,
 						cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -787,8 +783,7 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 
 	auto launch = [&](const Strip &st, StripBuf &b) -> int {
 		const bool packed = st.packed;
-		const bool wave = !(ctx->cfg.flags & SAB_FLAG_PANEL_KERNEL);
-		const int grid = wave ? ctx->wave_blocks[method][packed] : ctx->grid_blocks[method][packed];
+		const int grid = ctx->wave_blocks[method][packed];
 		const int a1 = st.a0 + st.an;
 		const size_t blk_elems = (size_t)(tri(a1) - tri(st.a0));
 		int rc = ensure(ctx, (void **)&b.blk, &b.blk_cap, std::max<size_t>(blk_elems, 1),
@@ -801,7 +796,7 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 			if (rc)
 				return rc;
 		}
-		const size_t bnd_block = (size_t)(sab::kThreads / 32) * bnd_rows * 32;
+		const size_t bnd_block = (size_t)bnd_rows * 32;
 		rc = ensure(ctx, (void **)&b.bnd, &b.bnd_cap, bnd_block * grid, sizeof(uint2));
 		if (rc)
 			return rc;
@@ -814,12 +809,10 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		p.tri0 = tri(st.a0);
 		p.blkT = (!triangular && matrix) ? b.blkT : nullptr;
 		p.chunk = packed ? 16 : 8;
-		p.nqb = (st.an + sab::kThreads - 1) / sab::kThreads;
 		p.nsc = (a1 + p.chunk - 1) / p.chunk;
 		p.counter = b.counter;
 		p.bnd = b.bnd;
 		p.bnd_block_stride = (int64_t)bnd_block;
-		p.bnd_rows = bnd_rows;
 		p.sub25 = ctx->d_sub25;
 		p.gapA = ctx->gapA;
 		p.gapE = ctx->gapE;
@@ -834,11 +827,8 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		if (S.launches == 0)
 			CU(cudaEventRecord(ctx->ev_span[0], b.stream));
 		CU(cudaEventRecord(b.ev_start, b.stream));
-		if (wave)
-			pick_wave_kernel(method, packed, ctx->cfg.flags & SAB_FLAG_WAVE_OCC4)<<<grid, sab::kWaveThreads, sab::kWaveSmemBytes,
-							   b.stream>>>(p);
-		else
-			pick_kernel(method, packed)<<<grid, sab::kThreads, sab::kSmemBytes, b.stream>>>(p);
+		pick_wave_kernel(method, packed, ctx->cfg.flags & SAB_FLAG_WAVE_OCC4)
+			<<<grid, sab::kWaveThreads, sab::kWaveSmemBytes, b.stream>>>(p);
 		CU(cudaGetLastError());
 		CU(cudaEventRecord(b.ev_done, b.stream));
 		S.launches++;

@@ -1,26 +1,38 @@
-// sab_wave.cuh -- systolic strip pipeline: the main sm_100a kernel of the all-vs-all DP fill.
+// sab_wave.cuh -- systolic strip pipeline: the sm_100a kernel of the all-vs-all DP fill.
 //
-// Same cell arithmetic and data layouts as sab_kernels.cuh (biased int16x2 lanes, DPX ops
-// on the alu pipe, carry-free 32-bit adds on the fma pipe, [column][letter] pair profile
-// in shared memory), different decomposition.  The first kernel gave every thread a whole
-// (query x subject pair) alignment and swept its 32-column register strips one after the
-// other, parking the strip boundary column (M+open, X per row) in global memory.  ncu on
-// C2 showed that boundary parking to be the limiter: 300 GB of DRAM traffic per launch and
-// long-scoreboard stalls on the boundary loads (profiles/r1_ncu_panel_kernel.md).
+// Decomposition
+//   * lane = QUERY sequence (DP rows, streamed 4 letters per step from the lane-interleaved
+//     `rowpack`), block = 32 queries x a chunk of SUBJECT PAIRS (DP columns): the two
+//     subjects of a pair sit in the low/high int16 halves of every register, so each DPX
+//     instruction updates two cells.
+//   * The 4 warps of a block work on the SAME 32 queries and on 4 CONSECUTIVE 32-column
+//     strips of the stream of strips of the item's subject pairs:
+//            step tau:   warp j computes row group (tau - j) mod G of its strip
+//     so warp j+1 is always one row group (4 rows) behind warp j, and the strip boundary
+//     column (V, X per row) travels warp j -> warp j+1 through an 8 KB shared-memory
+//     exchange buffer (the role the north star gives to __shfl_sync; lanes cannot be used
+//     for it because the conflict-free profile read needs all lanes of a warp on the same
+//     DP column).  Only the wrap-around warp 3 -> warp 0 (every 128 columns) goes through a
+//     per-block global buffer small enough to stay in L2.  The stream never drains inside
+//     an item: a warp that finishes a strip starts the strip four positions further on.
+//   * Each strip's substitution scores are expanded once into a shared-memory PAIR PROFILE
+//     prof[column][query letter] = (S[a0_col][q], S[a1_col][q]) - shift.  All 32 lanes read
+//     the same column with their own letter: 25 consecutive words, never a bank conflict.
 //
-// Here the 4 warps of a block work on the SAME 32 queries (lane = query) and on 4
-// CONSECUTIVE strips of the stream of strips of the item's subject pairs:
-//
-//        step tau:   warp j computes row group (tau - j) mod G of its strip
-//
-// so warp j+1 is always one row group (4 rows) behind warp j, and the boundary column
-// travels warp j -> warp j+1 through an 8 KB shared-memory exchange buffer (the role the
-// north star gives to __shfl_sync; lanes cannot be used for it because the conflict-free
-// profile read needs all lanes of a warp on the same DP column).  Only the wrap-around
-// warp 3 -> warp 0 (every 128 columns) still goes through global memory, one round later,
-// from a per-block buffer small enough to stay in L2.  The stream never drains inside an
-// item: when a warp finishes a strip it starts the strip four positions further on, of the
-// same or the next subject pair, so all four warps stay busy whatever the lengths are.
+// Cell arithmetic (per packed cell pair; alu = DPX on the 16-lane alu pipe, fma = IMAD)
+//   The stored matrix value V is a gap-skewed image of the reference's M/H so that the
+//   recurrences need as few adds as possible (g, o, e <= 0 are GAP_PEN/GAP_OPN/GAP_EXT):
+//     NW  V = H - g(r+c)      V = max3(Vdiag + (S - 2g), Vleft, Vup)               1 alu 1 fma
+//     GA  V = M - e(r+c)      X = max(Vleft + (o-e), Xleft)   Y = max(Vup + (o-e), Yup)
+//         (X, Y skewed too)   V = max3(Vdiag + (S - 2e), X, Y)                      3 alu 1 fma
+//     SW  V = M + o           Y = max3(Yup + e, Vup, 0)       X = max(Xleft + e, Vleft)
+//         (Y floored at 0)    M = max3(Vdiag + (S - o), X, Y)   V = M + o           3.5 alu 3 fma
+//   NW/GA borders become constants (0 resp. o-e) and the score is V + g|e * (Lq + Ls).
+//   SW keeps the unskewed form because its zero floor would turn into a per-cell value.
+//   A 4-row group is issued in ANTI-DIAGONAL order (row k works on column t-k at time t):
+//   the 2-3 instruction dependency chain of a cell is interleaved with three independent
+//   ones, which is what lets 3 resident warps per scheduler keep the alu pipe busy
+//   (profiles/r1_ncu_wave_v1.md shows the serial order stalling at 65 % alu).
 //
 // One __syncthreads per step (4 rows x 32 columns x 2 cells per thread).
 #pragma once
@@ -45,6 +57,60 @@ struct WaveSmem {
 };
 constexpr int kWaveSmemBytes = (int)sizeof(WaveSmem);
 
+// what the profile entries are shifted by (host: sub25 = S - shift)
+__host__ __device__ inline int profile_shift(int method, int gapA, int gapE)
+{
+	return method == M_NW ? 2 * gapA : method == M_GA ? 2 * gapE : gapA;
+}
+
+// Per-launch constants of the cell update, in the lane format of VOps<PACKED>.
+template <int METHOD, bool PACKED> struct CellK {
+	uint32_t one; // IMAD multiplier (uniform register)
+	uint32_t lG; // GA: lane(o - e); SW: lane(e)
+	uint32_t dE; // SW: 32-bit-add form of "+ e"
+	uint32_t dA; // SW: 32-bit-add form of "+ o"
+	uint32_t ZERO; // SW floor
+	int gE; // SW int32: raw extend
+};
+
+// One DP cell.  V = stored value of this column (in: row above, out: this row),
+// Yc = vertical-gap state of the column, ml/x = left neighbour's V / horizontal-gap state,
+// dg = diagonal neighbour's V, s = profile entry.  Returns M of the cell (SW maximum).
+template <int METHOD, bool PACKED>
+__device__ __forceinline__ uint32_t cell(const CellK<METHOD, PACKED> &k, uint32_t &V, uint32_t &Yc,
+					 uint32_t &ml, uint32_t &x, uint32_t &dg, const uint32_t s)
+{
+	using O = VOps<PACKED>;
+	const uint32_t tt = V;
+	const uint32_t d = O::addw(dg, s, k.one); // fma pipe
+	uint32_t m;
+	if (METHOD == M_NW) {
+		m = O::max3(d, ml, tt);
+		ml = m;
+	} else if (METHOD == M_GA) {
+		const uint32_t y = O::addmax(tt, k.lG, Yc);
+		x = O::addmax(ml, k.lG, x);
+		m = O::max3(d, x, y);
+		Yc = y;
+		ml = m;
+	} else {
+		uint32_t y;
+		if (PACKED) {
+			const uint32_t ye = O::addw(Yc, k.dE, k.one); // fma pipe
+			y = O::max3(ye, tt, k.ZERO);
+		} else {
+			y = (uint32_t)__viaddmax_s32_relu((int)Yc, k.gE, (int)tt);
+		}
+		x = O::addmax(x, k.lG, ml);
+		m = O::max3(d, x, y);
+		Yc = y;
+		ml = O::addw(m, k.dA, k.one); // fma pipe
+	}
+	dg = tt;
+	V = ml;
+	return m;
+}
+
 template <int METHOD, bool PACKED, int MINB>
 __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const TileParams p)
 {
@@ -66,12 +132,24 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 	const int nqg = (p.a_n + 31) >> 5;
 	const int nitems = nqg * p.nsc;
 	const int gA = p.gapA, gE = p.gapE;
-	const uint32_t one = p.one;
-	const uint32_t dA = O::delta(gA);
-	const uint32_t dE = O::delta(gE);
-	const uint32_t lE = O::lane(gE);
-	const uint32_t NEG = O::neg_inf(gE);
-	const uint32_t ZERO = O::bcast(0);
+
+	CellK<METHOD, PACKED> ck;
+	ck.one = p.one;
+	ck.lG = O::lane(METHOD == M_GA ? gA - gE : gE);
+	ck.dE = O::delta(gE);
+	ck.dA = O::delta(gA);
+	ck.ZERO = O::bcast(0);
+	ck.gE = gE;
+	// -inf stand-in.  NW/GA never add to it; SW adds e once, so NEG + e == biased 0 there.
+	const uint32_t NEG = PACKED ? (METHOD == M_SW ? O::lane(-gE) : 0u) : O::neg_inf(gE);
+	// Borders in stored coordinates (header comment): every border cell holds the same value.
+	//   NW  H[0][c] = cg, H[r][0] = rg                          -> V = 0        (nw.c:13-17)
+	//   GA  M[0][c] = o+(c-1)e, M[r][0] = o+(r-1)e, M[0][0] = 0 -> V = o-e, 0   (ga.c:23-38)
+	//   SW  M = 0 on both borders                               -> V = o        (sw.c:18-30)
+	const int vb = METHOD == M_NW ? 0 : METHOD == M_GA ? gA - gE : gA;
+	const int v00 = METHOD == M_SW ? gA : 0;
+	const uint32_t VB = O::bcast(vb);
+	const int gS = METHOD == M_NW ? gA : gE; // score = V + gS * (Lq + Ls) for NW/GA
 
 	for (;;) {
 		__syncthreads(); // previous item fully done
@@ -172,8 +250,8 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 		int tau_mod = 0, tau_round = 0;
 		int d_s = -1, d_c0 = 0, d_l0 = 0, d_l1 = 0, d_ps = 0;
 		bool first = false, last = false;
-		uint32_t Mo[K], Y[K];
-		uint32_t diag = 0, bl = 0, dstep = 0, best = ZERO;
+		uint32_t V[K], Y[K];
+		uint32_t diag = 0, bestA = ck.ZERO, bestB = ck.ZERO;
 		const uint32_t *prof_s = sm.prof[0][warp][0];
 		const int T = R * G + (kWaveWarps - 1);
 
@@ -182,7 +260,7 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 				build(tau_round + 1);
 
 			if (u >= 0 && rho < R) {
-				if (g == 0) { // start of a strip
+				if (g == 0) { // start of a strip: DP row 0 in stored coordinates
 					const int *d = sm.desc[rho & 1][warp];
 					d_s = d[0];
 					d_c0 = d[1];
@@ -193,97 +271,30 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 					first = d_c0 == 0;
 					last = d_c0 + K >= d_Lp;
 					prof_s = sm.prof[rho & 1][warp][0];
-					// Row 0 of the DP (borders), see run_strip() in sab_kernels.cuh
-					int m0, st, d0, b0;
-					if (METHOD == M_NW) {
-						m0 = (d_c0 + 2) * gA;
-						st = gA;
-						d0 = (d_c0 + 1) * gA;
-						b0 = 2 * gA;
-					} else if (METHOD == M_GA) {
-						m0 = 2 * gA + d_c0 * gE;
-						st = gE;
-						d0 = d_c0 ? 2 * gA + (d_c0 - 1) * gE : gA;
-						b0 = 2 * gA;
-					} else {
-						m0 = gA;
-						st = 0;
-						d0 = gA;
-						b0 = gA;
-					}
-					dstep = O::delta(st);
-					Mo[0] = O::bcast(m0);
-					Y[0] = (METHOD == M_SW && PACKED) ? ZERO : NEG;
+					const uint32_t y0 = (METHOD == M_SW && PACKED) ? ck.ZERO : NEG;
 #pragma unroll
-					for (int c = 1; c < K; c++) {
-						Mo[c] = Mo[c - 1] + dstep;
-						Y[c] = Y[0];
+					for (int c = 0; c < K; c++) {
+						V[c] = VB;
+						Y[c] = y0;
 					}
-					diag = O::bcast(d0);
-					bl = O::bcast(b0);
-					best = ZERO;
+					diag = first ? O::bcast(v00) : VB;
+					bestA = bestB = ck.ZERO;
 					if (METHOD == M_SW && first && d_s >= 0)
-						sm.sbest[d_ps][lane] = ZERO;
+						sm.sbest[d_ps][lane] = ck.ZERO;
 				}
 				const int r0 = g * kGroup;
 				if (d_s >= 0 && r0 < Lq) {
-					// One DP row of the strip: boundary (ml, x) of the column to the left in,
-					// boundary of the strip's last column out.
-					auto row = [&](uint32_t ml, uint32_t x, const uint32_t qoff) -> uint2 {
-						const uint32_t *pq = reinterpret_cast<const uint32_t *>(
-							reinterpret_cast<const char *>(prof_s) + qoff);
-						uint32_t dg = diag;
-						diag = ml;
-						uint32_t mprev = 0;
-#pragma unroll
-						for (int c = 0; c < K; c++) {
-							const uint32_t s = pq[c * kProfStride];
-							const uint32_t tt = Mo[c];
-							const uint32_t d = O::addw(dg, s, one); // fma pipe
-							uint32_t m;
-							if (METHOD == M_NW) {
-								m = O::max3(d, ml, tt);
-							} else {
-								uint32_t y;
-								if (METHOD == M_SW) {
-									if (PACKED) {
-										const uint32_t ye = O::addw(Y[c], dE, one);
-										y = O::max3(ye, tt, ZERO);
-									} else {
-										y = (uint32_t)__viaddmax_s32_relu((int)Y[c], gE, (int)tt);
-									}
-								} else {
-									y = O::addmax(Y[c], lE, tt);
-								}
-								x = O::addmax(x, lE, ml);
-								m = O::max3(d, x, y);
-								Y[c] = y;
-							}
-							if (METHOD == M_SW) {
-								if (c & 1)
-									best = O::max3(best, mprev, m);
-								else
-									mprev = m;
-							}
-							ml = O::addw(m, dA, one); // fma pipe
-							dg = tt;
-							Mo[c] = ml;
-						}
-						return make_uint2(ml, x);
-					};
 					const uint32_t w = rowp[g * 32];
 					const uint2 *xin = &sm.xch[(tau - 1) & 1][warp ? warp - 1 : 0][0][lane];
 					uint2 *xout = &sm.xch[tau & 1][warp < kWaveWarps - 1 ? warp : 0][0][lane];
 					const bool from_g = warp == 0, to_g = warp == kWaveWarps - 1;
 					if (r0 + kGroup <= Lq) {
-						// ---- full group: straight-line code, no per-row control flow ----
+						// ---- full group: straight-line code, rows issued anti-diagonally ----
 						uint2 b[kGroup];
 						if (first) {
 #pragma unroll
-							for (int k = 0; k < kGroup; k++) {
-								b[k] = make_uint2(bl, NEG);
-								bl += dstep;
-							}
+							for (int k = 0; k < kGroup; k++)
+								b[k] = make_uint2(VB, NEG);
 						} else if (from_g) {
 #pragma unroll
 							for (int k = 0; k < kGroup; k++)
@@ -293,18 +304,49 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 							for (int k = 0; k < kGroup; k++)
 								b[k] = xin[k * 32];
 						}
+						uint32_t ml[kGroup], x[kGroup], dg[kGroup], mprev[kGroup];
+						const uint32_t *pq[kGroup];
 #pragma unroll
-						for (int k = 0; k < kGroup; k++)
-							b[k] = row(b[k].x, b[k].y, (w >> (8 * k)) & 0xffu);
+						for (int k = 0; k < kGroup; k++) {
+							ml[k] = b[k].x;
+							x[k] = b[k].y;
+							dg[k] = k ? b[k - 1].x : diag;
+							mprev[k] = 0;
+							pq[k] = reinterpret_cast<const uint32_t *>(
+								reinterpret_cast<const char *>(prof_s) +
+								((w >> (8 * k)) & 0xffu));
+						}
+						diag = b[kGroup - 1].x;
+#pragma unroll
+						for (int tt = 0; tt < K + kGroup - 1; tt++) {
+#pragma unroll
+							for (int k = 0; k < kGroup; k++) {
+								const int c = tt - k;
+								if (c < 0 || c >= K)
+									continue;
+								const uint32_t m = cell<METHOD, PACKED>(
+									ck, V[c], Y[c], ml[k], x[k], dg[k], pq[k][c * kProfStride]);
+								if (METHOD == M_SW) {
+									if (c & 1) {
+										if (k & 1)
+											bestB = O::max3(bestB, mprev[k], m);
+										else
+											bestA = O::max3(bestA, mprev[k], m);
+									} else {
+										mprev[k] = m;
+									}
+								}
+							}
+						}
 						if (!last) {
 							if (to_g) {
 #pragma unroll
 								for (int k = 0; k < kGroup; k++)
-									gfr[(r0 + k) * 32] = b[k];
+									gfr[(r0 + k) * 32] = make_uint2(ml[k], x[k]);
 							} else {
 #pragma unroll
 								for (int k = 0; k < kGroup; k++)
-									xout[k * 32] = b[k];
+									xout[k * 32] = make_uint2(ml[k], x[k]);
 							}
 						}
 					} else {
@@ -312,18 +354,30 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 #pragma unroll 1
 						for (int k = 0; r0 + k < Lq; k++) {
 							uint2 b;
-							if (first) {
-								b = make_uint2(bl, NEG);
-								bl += dstep;
-							} else {
+							if (first)
+								b = make_uint2(VB, NEG);
+							else
 								b = from_g ? gfr[(r0 + k) * 32] : xin[k * 32];
+							uint32_t ml = b.x, x = b.y, dg = diag, mprev = 0;
+							diag = b.x;
+							const uint32_t *pq = reinterpret_cast<const uint32_t *>(
+								reinterpret_cast<const char *>(prof_s) + ((w >> (8 * k)) & 0xffu));
+#pragma unroll
+							for (int c = 0; c < K; c++) {
+								const uint32_t m = cell<METHOD, PACKED>(ck, V[c], Y[c], ml, x, dg,
+													pq[c * kProfStride]);
+								if (METHOD == M_SW) {
+									if (c & 1)
+										bestA = O::max3(bestA, mprev, m);
+									else
+										mprev = m;
+								}
 							}
-							b = row(b.x, b.y, (w >> (8 * k)) & 0xffu);
 							if (!last) {
 								if (to_g)
-									gfr[(r0 + k) * 32] = b;
+									gfr[(r0 + k) * 32] = make_uint2(ml, x);
 								else
-									xout[k * 32] = b;
+									xout[k * 32] = make_uint2(ml, x);
 							}
 						}
 					}
@@ -333,7 +387,7 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 						bool have0 = false, have1 = false;
 						if (METHOD == M_SW) {
 							uint32_t acc = sm.sbest[d_ps][lane];
-							acc = O::max3(acc, best, best);
+							acc = O::max3(acc, bestA, bestB);
 							if (last) {
 								sc0 = O::lo(acc);
 								sc1 = O::hi(acc);
@@ -343,14 +397,16 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 								sm.sbest[d_ps][lane] = acc;
 							}
 						} else {
+							// M[Lq][Ls] = V + gS * (Lq + Ls), picked out of the register strip
+							// that holds the subject's last column (block-uniform index)
 							const int cap0 = d_l0 - 1 - d_c0, cap1 = d_l1 - 1 - d_c0;
 							if (cap0 >= 0 && cap0 < K) {
 								uint32_t v = 0;
 #pragma unroll
 								for (int c = 0; c < K; c++)
 									if (c == cap0)
-										v = Mo[c];
-								sc0 = O::lo(v) - gA;
+										v = V[c];
+								sc0 = O::lo(v) + gS * (Lq + d_l0);
 								have0 = true;
 							}
 							if (PACKED && cap1 >= 0 && cap1 < K) {
@@ -358,8 +414,8 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 #pragma unroll
 								for (int c = 0; c < K; c++)
 									if (c == cap1)
-										v = Mo[c];
-								sc1 = O::hi(v) - gA;
+										v = V[c];
+								sc1 = O::hi(v) + gS * (Lq + d_l1);
 								have1 = true;
 							}
 						}
