@@ -69,9 +69,8 @@ typedef struct sab_meta {
 enum sab_flags {
 	SAB_FLAG_FORCE_INT32 = 1, /* testing: never use the packed int16x2 kernels */
 	SAB_FLAG_FORCE_INT16 = 2, /* testing: skip the a-priori range test (SW still re-runs) */
-	SAB_FLAG_PANEL_KERNEL = 4, /* use the first-generation one-thread-per-alignment kernel
-				    * instead of the systolic strip pipeline (comparison runs) */
-	SAB_FLAG_WAVE_OCC4 = 8, /* tuning: 128-register build of the pipeline kernel (4 blocks/SM) */
+	SAB_FLAG_WAVE_OCC3 = 8, /* tuning: <=170-register build of the kernel (3 blocks/SM instead
+				 * of the default 128-register build with 4 blocks/SM) */
 };
 
 typedef struct sab_config {

@@ -14,8 +14,7 @@ SAB_OK = 0
 SAB_NW, SAB_GA, SAB_SW = 0, 1, 2
 SAB_FLAG_FORCE_INT32 = 1
 SAB_FLAG_FORCE_INT16 = 2
-SAB_FLAG_PANEL_KERNEL = 4
-SAB_FLAG_WAVE_OCC4 = 8
+SAB_FLAG_WAVE_OCC3 = 8
 STATUS = {0: "SAB_OK", -1: "SAB_ERR_ARG", -2: "SAB_ERR_NODEVICE", -3: "SAB_ERR_CUDA",
           -4: "SAB_ERR_NOMEM", -5: "SAB_ERR_STATE", -6: "SAB_ERR_OVERFLOW"}
 

@@ -130,9 +130,9 @@ template <int MINB> tile_kernel_t pick_wave_kernel_t(int method, bool packed)
 	}
 }
 
-tile_kernel_t pick_wave_kernel(int method, bool packed, bool occ4)
+tile_kernel_t pick_wave_kernel(int method, bool packed, bool occ3)
 {
-	return occ4 ? pick_wave_kernel_t<4>(method, packed) : pick_wave_kernel_t<3>(method, packed);
+	return occ3 ? pick_wave_kernel_t<3>(method, packed) : pick_wave_kernel_t<4>(method, packed);
 }
 
 void free_seqs(sab_ctx *c)
@@ -413,7 +413,7 @@ int sab_create(sab_ctx **out, const sab_config *cfg)
 	for (int m = 0; m < 3; m++)
 		for (int pk = 0; pk < 2; pk++) {
 			int occ = 0;
-			tile_kernel_t wk = pick_wave_kernel(m, pk, ctx->cfg.flags & SAB_FLAG_WAVE_OCC4);
+			tile_kernel_t wk = pick_wave_kernel(m, pk, ctx->cfg.flags & SAB_FLAG_WAVE_OCC3);
 			CU(cudaFuncSetAttribute((const void *)wk,
 						cudaFuncAttributeMaxDynamicSharedMemorySize,
 						sab::kWaveSmemBytes));
@@ -553,12 +553,16 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 			gmax = std::max(gmax, slot_len[s]);
 		rows4 += (gmax + 3) / 4 + 2; // + prefetch slack
 	}
-	std::vector<uint32_t> rowpack((size_t)rows4 * 32, 0);
+	// rows past a sequence's end hold the pad letter (24): SW sweeps them (sab_wave.cuh)
+	std::vector<uint32_t> rowpack((size_t)rows4 * 32, 0x60606060u);
 	for (int32_t s = 0; s < num; s++) {
 		const uint8_t *src = col_bytes.data() + col_off[s];
 		uint32_t *dst = rowpack.data() + grp_off[s >> 5] * 32 + (s & 31);
-		for (int32_t r = 0; r < slot_len[s]; r++)
-			dst[(size_t)(r >> 2) * 32] |= (uint32_t)(src[r] * 4) << (8 * (r & 3));
+		for (int32_t r = 0; r < slot_len[s]; r++) {
+			uint32_t &wd = dst[(size_t)(r >> 2) * 32];
+			const int sh = 8 * (r & 3);
+			wd = (wd & ~(0xffu << sh)) | ((uint32_t)(src[r] * 4) << sh);
+		}
 	}
 
 	CU(cudaMalloc(&ctx->d_slot_len, sizeof(int32_t) * num));
@@ -827,7 +831,7 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		if (S.launches == 0)
 			CU(cudaEventRecord(ctx->ev_span[0], b.stream));
 		CU(cudaEventRecord(b.ev_start, b.stream));
-		pick_wave_kernel(method, packed, ctx->cfg.flags & SAB_FLAG_WAVE_OCC4)
+		pick_wave_kernel(method, packed, ctx->cfg.flags & SAB_FLAG_WAVE_OCC3)
 			<<<grid, sab::kWaveThreads, sab::kWaveSmemBytes, b.stream>>>(p);
 		CU(cudaGetLastError());
 		CU(cudaEventRecord(b.ev_done, b.stream));

@@ -39,11 +39,14 @@
 
 #include "sab_kernels.cuh"
 
+#include <type_traits>
+
 namespace sab {
 
 constexpr int kWaveWarps = 4;
 constexpr int kWaveThreads = kWaveWarps * 32;
-constexpr int kGroup = 4; // rows per step
+constexpr int kGroup = 8; // rows per step (multiple of 4: rowpack holds 4 letters per word)
+constexpr int kGroupWords = kGroup / 4;
 constexpr int kBestSlots = 16; // subject pairs whose SW maxima can be in flight
 constexpr int kMinSteps = 6; // steps per round (>= 4 for the double-buffered staging)
 
@@ -284,43 +287,49 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 				}
 				const int r0 = g * kGroup;
 				if (d_s >= 0 && r0 < Lq) {
-					const uint32_t w = rowp[g * 32];
+					uint32_t w[kGroupWords];
+#pragma unroll
+					for (int i = 0; i < kGroupWords; i++)
+						w[i] = rowp[(g * kGroupWords + i) * 32];
 					const uint2 *xin = &sm.xch[(tau - 1) & 1][warp ? warp - 1 : 0][0][lane];
 					uint2 *xout = &sm.xch[tau & 1][warp < kWaveWarps - 1 ? warp : 0][0][lane];
 					const bool from_g = warp == 0, to_g = warp == kWaveWarps - 1;
-					if (r0 + kGroup <= Lq) {
-						// ---- full group: straight-line code, rows issued anti-diagonally ----
-						uint2 b[kGroup];
+					// NR rows [k0, k0 + NR) of the group as straight-line code, issued
+					// anti-diagonally: at time tt row k works on column tt - k.
+					auto run_rows = [&](auto nr_c, const int k0) {
+						constexpr int NR = decltype(nr_c)::value;
+						uint2 b[NR];
 						if (first) {
 #pragma unroll
-							for (int k = 0; k < kGroup; k++)
+							for (int k = 0; k < NR; k++)
 								b[k] = make_uint2(VB, NEG);
 						} else if (from_g) {
 #pragma unroll
-							for (int k = 0; k < kGroup; k++)
-								b[k] = gfr[(r0 + k) * 32];
+							for (int k = 0; k < NR; k++)
+								b[k] = gfr[(r0 + k0 + k) * 32];
 						} else {
 #pragma unroll
-							for (int k = 0; k < kGroup; k++)
-								b[k] = xin[k * 32];
+							for (int k = 0; k < NR; k++)
+								b[k] = xin[(k0 + k) * 32];
 						}
-						uint32_t ml[kGroup], x[kGroup], dg[kGroup], mprev[kGroup];
-						const uint32_t *pq[kGroup];
+						uint32_t ml[NR], x[NR], dg[NR], mprev[NR];
+						const uint32_t *pq[NR];
 #pragma unroll
-						for (int k = 0; k < kGroup; k++) {
+						for (int k = 0; k < NR; k++) {
 							ml[k] = b[k].x;
 							x[k] = b[k].y;
 							dg[k] = k ? b[k - 1].x : diag;
 							mprev[k] = 0;
+							const int kk = k0 + k;
+							const uint32_t wk = (kGroupWords > 1 && (kk & 4)) ? w[kGroupWords - 1] : w[0];
 							pq[k] = reinterpret_cast<const uint32_t *>(
-								reinterpret_cast<const char *>(prof_s) +
-								((w >> (8 * k)) & 0xffu));
+								reinterpret_cast<const char *>(prof_s) + ((wk >> (8 * (kk & 3))) & 0xffu));
 						}
-						diag = b[kGroup - 1].x;
+						diag = b[NR - 1].x;
 #pragma unroll
-						for (int tt = 0; tt < K + kGroup - 1; tt++) {
+						for (int tt = 0; tt < K + NR - 1; tt++) {
 #pragma unroll
-							for (int k = 0; k < kGroup; k++) {
+							for (int k = 0; k < NR; k++) {
 								const int c = tt - k;
 								if (c < 0 || c >= K)
 									continue;
@@ -341,45 +350,28 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 						if (!last) {
 							if (to_g) {
 #pragma unroll
-								for (int k = 0; k < kGroup; k++)
-									gfr[(r0 + k) * 32] = make_uint2(ml[k], x[k]);
+								for (int k = 0; k < NR; k++)
+									gfr[(r0 + k0 + k) * 32] = make_uint2(ml[k], x[k]);
 							} else {
 #pragma unroll
-								for (int k = 0; k < kGroup; k++)
-									xout[k * 32] = make_uint2(ml[k], x[k]);
+								for (int k = 0; k < NR; k++)
+									xout[(k0 + k) * 32] = make_uint2(ml[k], x[k]);
 							}
 						}
+					};
+					// SW runs its last group in full: the rows past Lq hold the pad letter
+					// (score 0 against everything), which can never raise the running maximum.
+					// NW/GA need V at row Lq exactly: their 1..7 tail rows go as 4 + 2 + 1.
+					if (METHOD == M_SW || r0 + kGroup <= Lq) {
+						run_rows(std::integral_constant<int, kGroup>{}, 0);
 					} else {
-						// ---- 1..3 tail rows of this query ----
-#pragma unroll 1
-						for (int k = 0; r0 + k < Lq; k++) {
-							uint2 b;
-							if (first)
-								b = make_uint2(VB, NEG);
-							else
-								b = from_g ? gfr[(r0 + k) * 32] : xin[k * 32];
-							uint32_t ml = b.x, x = b.y, dg = diag, mprev = 0;
-							diag = b.x;
-							const uint32_t *pq = reinterpret_cast<const uint32_t *>(
-								reinterpret_cast<const char *>(prof_s) + ((w >> (8 * k)) & 0xffu));
-#pragma unroll
-							for (int c = 0; c < K; c++) {
-								const uint32_t m = cell<METHOD, PACKED>(ck, V[c], Y[c], ml, x, dg,
-													pq[c * kProfStride]);
-								if (METHOD == M_SW) {
-									if (c & 1)
-										bestA = O::max3(bestA, mprev, m);
-									else
-										mprev = m;
-								}
-							}
-							if (!last) {
-								if (to_g)
-									gfr[(r0 + k) * 32] = make_uint2(ml, x);
-								else
-									xout[k * 32] = make_uint2(ml, x);
-							}
-						}
+						const int nv = Lq - r0;
+						if (nv & 4)
+							run_rows(std::integral_constant<int, 4>{}, 0);
+						if (nv & 2)
+							run_rows(std::integral_constant<int, 2>{}, nv & 4);
+						if (nv & 1)
+							run_rows(std::integral_constant<int, 1>{}, nv & 6);
 					}
 					// ---- my last row of this strip: results ------------------------
 					if (Lq <= r0 + kGroup) {
