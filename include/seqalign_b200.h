@@ -69,8 +69,8 @@ typedef struct sab_meta {
 enum sab_flags {
 	SAB_FLAG_FORCE_INT32 = 1, /* testing: never use the packed int16x2 kernels */
 	SAB_FLAG_FORCE_INT16 = 2, /* testing: skip the a-priori range test (SW still re-runs) */
-	SAB_FLAG_WAVE_OCC3 = 8, /* tuning: <=170-register build of the kernel (3 blocks/SM instead
-				 * of the default 128-register build with 4 blocks/SM) */
+	SAB_FLAG_STRIP32 = 8, /* testing/tuning: always use the 32-column register-strip kernel */
+	SAB_FLAG_STRIP16 = 16, /* testing/tuning: always use the 16-column register-strip kernel */
 };
 
 typedef struct sab_config {

@@ -6,6 +6,7 @@ raises -- there is no Python / CPU fallback for the alignment path.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 from .build import LIB
@@ -14,7 +15,8 @@ SAB_OK = 0
 SAB_NW, SAB_GA, SAB_SW = 0, 1, 2
 SAB_FLAG_FORCE_INT32 = 1
 SAB_FLAG_FORCE_INT16 = 2
-SAB_FLAG_WAVE_OCC3 = 8
+SAB_FLAG_STRIP32 = 8
+SAB_FLAG_STRIP16 = 16
 STATUS = {0: "SAB_OK", -1: "SAB_ERR_ARG", -2: "SAB_ERR_NODEVICE", -3: "SAB_ERR_CUDA",
           -4: "SAB_ERR_NOMEM", -5: "SAB_ERR_STATE", -6: "SAB_ERR_OVERFLOW"}
 
@@ -82,7 +84,7 @@ def load(path: Path | None = None) -> C.CDLL:
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = Path(path or LIB)
+    p = Path(path or os.environ.get("SAB_LIB") or LIB)  # SAB_LIB: tuning builds (tools/variants.sh)
     if not p.exists():
         raise RuntimeError(
             f"{p} is missing: build it with `python -m sequencealigner_b200.build` "

@@ -88,7 +88,7 @@ struct sab_ctx {
 	cudaStream_t copy_stream = nullptr;
 	cudaEvent_t ev_copy[2] = { nullptr, nullptr };
 	cudaEvent_t ev_span[2] = { nullptr, nullptr }; // first kernel start / last kernel end
-	int wave_blocks[3][2]{}; // [method][packed] resident persistent blocks of the kernel
+	int wave_blocks[3][2][2]{}; // [method][packed][narrow] resident persistent blocks
 	sab_stats stats{};
 };
 
@@ -118,21 +118,31 @@ int fail(sab_ctx *c, int code, const char *fmt, ...)
 
 typedef void (*tile_kernel_t)(const TileParams);
 
-template <int MINB> tile_kernel_t pick_wave_kernel_t(int method, bool packed)
+// Kernel variants: [narrow] strip width 32 (4 resident blocks/SM) or 16 (5 blocks/SM).
+constexpr int kStripWide = 32, kStripNarrow = 16;
+constexpr int kMinbWide = 4, kMinbNarrow = 5;
+
+template <int K, int MINB> tile_kernel_t pick_wave_kernel_t(int method, bool packed)
 {
 	switch (method * 2 + (packed ? 1 : 0)) {
-	case 0: return sab::sab_wave_kernel<sab::M_NW, false, MINB>;
-	case 1: return sab::sab_wave_kernel<sab::M_NW, true, MINB>;
-	case 2: return sab::sab_wave_kernel<sab::M_GA, false, MINB>;
-	case 3: return sab::sab_wave_kernel<sab::M_GA, true, MINB>;
-	case 4: return sab::sab_wave_kernel<sab::M_SW, false, MINB>;
-	default: return sab::sab_wave_kernel<sab::M_SW, true, MINB>;
+	case 0: return sab::sab_wave_kernel<sab::M_NW, false, K, MINB>;
+	case 1: return sab::sab_wave_kernel<sab::M_NW, true, K, MINB>;
+	case 2: return sab::sab_wave_kernel<sab::M_GA, false, K, MINB>;
+	case 3: return sab::sab_wave_kernel<sab::M_GA, true, K, MINB>;
+	case 4: return sab::sab_wave_kernel<sab::M_SW, false, K, MINB>;
+	default: return sab::sab_wave_kernel<sab::M_SW, true, K, MINB>;
 	}
 }
 
-tile_kernel_t pick_wave_kernel(int method, bool packed, bool occ3)
+tile_kernel_t pick_wave_kernel(int method, bool packed, bool narrow)
 {
-	return occ3 ? pick_wave_kernel_t<3>(method, packed) : pick_wave_kernel_t<4>(method, packed);
+	return narrow ? pick_wave_kernel_t<kStripNarrow, kMinbNarrow>(method, packed) :
+			pick_wave_kernel_t<kStripWide, kMinbWide>(method, packed);
+}
+
+int wave_smem_bytes(bool narrow)
+{
+	return narrow ? (int)sizeof(sab::WaveSmem<kStripNarrow>) : (int)sizeof(sab::WaveSmem<kStripWide>);
 }
 
 void free_seqs(sab_ctx *c)
@@ -412,16 +422,18 @@ int sab_create(sab_ctx **out, const sab_config *cfg)
 	CU(cudaMemcpy(ctx->d_sub25, ctx->sub25, sizeof ctx->sub25, cudaMemcpyHostToDevice));
 	for (int m = 0; m < 3; m++)
 		for (int pk = 0; pk < 2; pk++) {
-			int occ = 0;
-			tile_kernel_t wk = pick_wave_kernel(m, pk, ctx->cfg.flags & SAB_FLAG_WAVE_OCC3);
-			CU(cudaFuncSetAttribute((const void *)wk,
-						cudaFuncAttributeMaxDynamicSharedMemorySize,
-						sab::kWaveSmemBytes));
-			CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-				&occ, (const void *)wk, sab::kWaveThreads, sab::kWaveSmemBytes));
-			if (occ < 1)
-				return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
-			ctx->wave_blocks[m][pk] = occ * ctx->sm_count;
+			for (int nr = 0; nr < 2; nr++) {
+				int occ = 0;
+				tile_kernel_t wk = pick_wave_kernel(m, pk, nr);
+				CU(cudaFuncSetAttribute((const void *)wk,
+							cudaFuncAttributeMaxDynamicSharedMemorySize,
+							wave_smem_bytes(nr)));
+				CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+					&occ, (const void *)wk, sab::kWaveThreads, wave_smem_bytes(nr)));
+				if (occ < 1)
+					return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
+				ctx->wave_blocks[m][pk][nr] = occ * ctx->sm_count;
+			}
 		}
 	for (int i = 0; i < 2; i++) {
 		StripBuf &b = ctx->buf[i];
@@ -604,6 +616,7 @@ struct Strip {
 	int a0, an; // original index range == slot range
 	double cost; // sum len_q * sum len_s (approx. cells)
 	bool packed;
+	bool narrow; // 16-column register strips (short subjects)
 	int lq, ls; // longest query / subject
 };
 
@@ -644,6 +657,11 @@ void plan_strips(const sab_ctx *ctx, int nshards, std::vector<Strip> &strips, st
 		const double ls_sum = (double)ctx->len_prefix[s.a0] + 0.5 * lq_sum;
 		s.cost = lq_sum * ls_sum;
 		s.packed = !force32 && (force16 || int16_safe(ctx, s.lq, s.ls));
+		// strip width: padding a subject to 16 instead of 32 columns saves ~8 columns per
+		// subject, the narrow kernel costs ~4 % (profiles/r1_variants.md) -> narrow below ~160
+		const double mean_ls = (double)ctx->len_prefix[s.a0 + s.an] / (s.a0 + s.an);
+		s.narrow = (ctx->cfg.flags & SAB_FLAG_STRIP16) ||
+			   (!(ctx->cfg.flags & SAB_FLAG_STRIP32) && mean_ls < 160.0);
 	}
 	std::vector<double> cost(npanels);
 	for (int p = 0; p < npanels; p++)
@@ -787,7 +805,8 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 
 	auto launch = [&](const Strip &st, StripBuf &b) -> int {
 		const bool packed = st.packed;
-		const int grid = ctx->wave_blocks[method][packed];
+		const bool narrow = st.narrow;
+		const int grid = ctx->wave_blocks[method][packed][narrow];
 		const int a1 = st.a0 + st.an;
 		const size_t blk_elems = (size_t)(tri(a1) - tri(st.a0));
 		int rc = ensure(ctx, (void **)&b.blk, &b.blk_cap, std::max<size_t>(blk_elems, 1),
@@ -831,8 +850,8 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		if (S.launches == 0)
 			CU(cudaEventRecord(ctx->ev_span[0], b.stream));
 		CU(cudaEventRecord(b.ev_start, b.stream));
-		pick_wave_kernel(method, packed, ctx->cfg.flags & SAB_FLAG_WAVE_OCC3)
-			<<<grid, sab::kWaveThreads, sab::kWaveSmemBytes, b.stream>>>(p);
+		pick_wave_kernel(method, packed, narrow)
+			<<<grid, sab::kWaveThreads, wave_smem_bytes(narrow), b.stream>>>(p);
 		CU(cudaGetLastError());
 		CU(cudaEventRecord(b.ev_done, b.stream));
 		S.launches++;

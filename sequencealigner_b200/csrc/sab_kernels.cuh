@@ -30,7 +30,7 @@
 
 namespace sab {
 
-constexpr int kStrip = 32; // DP columns held in registers per strip
+constexpr int kStrip = 32; // widest register strip (DP columns per warp); subjects are padded to it at most
 constexpr int kLetters = 25; // 24 residues + 1 pad letter
 constexpr int kProfStride = 25; // words per profile column (coprime with 32 banks)
 

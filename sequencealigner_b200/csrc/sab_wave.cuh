@@ -45,20 +45,22 @@ namespace sab {
 
 constexpr int kWaveWarps = 4;
 constexpr int kWaveThreads = kWaveWarps * 32;
-constexpr int kGroup = 8; // rows per step (multiple of 4: rowpack holds 4 letters per word)
+#ifndef SAB_KGROUP
+#define SAB_KGROUP 8
+#endif
+constexpr int kGroup = SAB_KGROUP; // rows per step (multiple of 4: rowpack holds 4 letters per word)
 constexpr int kGroupWords = kGroup / 4;
 constexpr int kBestSlots = 16; // subject pairs whose SW maxima can be in flight
 constexpr int kMinSteps = 6; // steps per round (>= 4 for the double-buffered staging)
 
-struct WaveSmem {
-	uint32_t prof[2][kWaveWarps][kStrip][kProfStride]; // strip profiles, parity = round & 1
+template <int K> struct WaveSmem {
+	uint32_t prof[2][kWaveWarps][K][kProfStride]; // strip profiles, parity = round & 1
 	uint2 xch[2][kWaveWarps - 1][kGroup][32]; // boundary rows warp j -> j+1, parity = step & 1
 	uint32_t sbest[kBestSlots][32]; // SW running maxima per subject pair
 	int32_t ssub[kLetters * kLetters];
 	int desc[2][kWaveWarps][8]; // strip descriptors, parity = round & 1
 	int item;
 };
-constexpr int kWaveSmemBytes = (int)sizeof(WaveSmem);
 
 // what the profile entries are shifted by (host: sub25 = S - shift)
 __host__ __device__ inline int profile_shift(int method, int gapA, int gapE)
@@ -114,14 +116,15 @@ __device__ __forceinline__ uint32_t cell(const CellK<METHOD, PACKED> &k, uint32_
 	return m;
 }
 
-template <int METHOD, bool PACKED, int MINB>
+// K = DP columns a warp holds in registers (strip width): 32 for long subjects, 16 for short
+// ones (less column padding, 6 resident blocks per SM instead of 4).
+template <int METHOD, bool PACKED, int K, int MINB>
 __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const TileParams p)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
-	WaveSmem &sm = *reinterpret_cast<WaveSmem *>(smem_raw);
+	WaveSmem<K> &sm = *reinterpret_cast<WaveSmem<K> *>(smem_raw);
 	using O = VOps<PACKED>;
 	constexpr int NS = PACKED ? 2 : 1;
-	constexpr int K = kStrip;
 	const int tid = threadIdx.x;
 	const int lane = tid & 31;
 	const int warp = tid >> 5;
@@ -237,12 +240,14 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 				if (PACKED && c < my_l1)
 					a1 = p.seqs.col_bytes[p.seqs.col_off[my_s + 1] + c];
 			}
-			uint32_t *dst = sm.prof[pb][warp][lane];
-			const int32_t *r0 = sm.ssub + a0 * kLetters;
-			const int32_t *r1 = sm.ssub + a1 * kLetters;
+			if (K == 32 || lane < K) { // lane = column of the strip
+				uint32_t *dst = sm.prof[pb][warp][lane < K ? lane : 0];
+				const int32_t *r0 = sm.ssub + a0 * kLetters;
+				const int32_t *r1 = sm.ssub + a1 * kLetters;
 #pragma unroll 5
-			for (int q = 0; q < kLetters; q++)
-				dst[q] = O::delta2(r0[q], r1[q]);
+				for (int q = 0; q < kLetters; q++)
+					dst[q] = O::delta2(r0[q], r1[q]);
+			}
 		};
 
 		build(0);

@@ -48,7 +48,9 @@ def test_golden_all_tables(flags):
 
 
 @pytest.mark.parametrize("method,kw", METHODS)
-@pytest.mark.parametrize("flags", [0, capi.SAB_FLAG_FORCE_INT32])
+@pytest.mark.parametrize("flags", [0, capi.SAB_FLAG_FORCE_INT32, capi.SAB_FLAG_STRIP16,
+                                   capi.SAB_FLAG_STRIP32,
+                                   capi.SAB_FLAG_STRIP16 | capi.SAB_FLAG_FORCE_INT32])
 def test_vs_oracle_mixed_lengths(oracle_mod, method, kw, flags):
     """ragged lengths 1..420 across several panels, strips and register windows"""
     rng = np.random.default_rng(5)
@@ -60,7 +62,7 @@ def test_vs_oracle_mixed_lengths(oracle_mod, method, kw, flags):
     want, _ = oracle_mod.align_all(cfg.resolve(), store, triangular=True)
     got, st = gpu_scores(cfg, store, triangular=True, panel=256, flags=flags)
     assert st["pairs"] == store.pairs() and st["cells"] == store.cells()
-    assert (st["tiles_int32"] > 0) == bool(flags)
+    assert (st["tiles_int32"] > 0) == bool(flags & capi.SAB_FLAG_FORCE_INT32)
     bad = np.flatnonzero(got != want)
     assert bad.size == 0, (bad[:10], got[bad[:10]], want[bad[:10]])
 
