@@ -14,8 +14,8 @@ JSON keys (one line, rank 0):
              (CUDA events recorded by the library on its own streams), max over ranks
   e2e        GCUPS through the C ABI with HOST buffers: sab_upload (pack + H2D) and
              sab_align into a host matrix (D2H + host scatter) inside the timed region
-  roofline   dominant kernel vs the integer-pipe peak measured on this box
-             (tools/pipe_peak.cu); HBM shown non-binding next to it
+  roofline   dominant kernel vs the integer issue peak (DPX + IMAD rates) measured on this
+             box in the same run (tools/pipe_peak.cu); HBM shown non-binding next to it
   cpu_baseline  the reference's own CPU code (oracle/_ref/seqalign) on this box's host
              cores, bounded sample of the same workload
 """
@@ -38,8 +38,8 @@ sys.path.insert(0, str(ROOT))
 
 # algorithmic integer lane-instructions per DP cell
 INSTR_PER_CELL = {"nw": 1.5, "ga": 3.0, "sw": 3.5}
-# what the kernels actually issue per cell on the integer pipes
-EXEC_INSTR_PER_CELL = {"nw": 1.5, "ga": 2.5, "sw": 2.75}
+# DPX (alu-pipe) instructions the kernel issues per cell
+ALU_INSTR_PER_CELL = {"nw": 0.5, "ga": 1.5, "sw": 1.75}
 
 
 def dist_env():
@@ -281,6 +281,7 @@ def run_ours(args):
     step_ms, step_cells = reduce_over_ranks(dev_ms / args.steps, my_cells // args.steps)
     value = step_cells / (step_ms * 1e-3) / 1e9
     kern_step_ms, _ = reduce_over_ranks(kernel_ms / args.steps, 0)
+    launches_value_leg = launches
 
     # ---- end to end through the C ABI with host buffers (`e2e`) ------------------------
     for _ in range(min(args.warmup, 1)):
@@ -307,12 +308,18 @@ def run_ours(args):
             dist.destroy_process_group()
         return 0
 
-    # ---- roofline of the dominant kernel (sab_tile_kernel<method, int16x2>) ------------
+    # ---- roofline of the dominant kernel (sab_wave_kernel<method, int16x2, K>) ------------
+    # Bound: SM integer issue.  achieved = cells/s x the ALGORITHMIC
+    # lane-instructions per cell of SURVEY.md section 8d; peak = DPX (alu pipe) + IMAD (fma
+    # pipe) lane-instruction rates measured on this box right now by tools/pipe_peak.cu.
     peaks = measure_pipe_peak(local_rank) or {}
     method = c["method"]
-    alu_peak = max(peaks.get("viaddmnmx_s16x2", 0.0), peaks.get("vimnmx3_s16x2", 0.0)) or None
+    dpx_peak = max(peaks.get("viaddmnmx_u16x2", 0.0), peaks.get("vimnmx3_u16x2", 0.0)) or None
+    imad_peak = peaks.get("imad") or None
+    int_peak = (dpx_peak + imad_peak) if dpx_peak and imad_peak else None
     cells_per_s_gpu = step_cells / n_gpus / (kern_step_ms * 1e-3)
     achieved = cells_per_s_gpu * INSTR_PER_CELL[method] / 1e12
+    alu_issued = cells_per_s_gpu * ALU_INSTR_PER_CELL[method] / 1e12
     traffic = None
     tf = ROOT / "profiles" / "traffic.json"
     if tf.exists():
@@ -331,14 +338,19 @@ def run_ours(args):
     bits = 5 if c["alphabet"] != "ACGT" else 2
     alg_bytes = float(store.pairs()) * 4 + float(store.lengths.sum()) * bits / 8 * 2
     roofline = {
-        "bound": "int_alu", "kernel": f"sab_tile_kernel<{method},int16x2>",
-        "achieved": achieved, "peak": alu_peak, "unit": "T lane-instr/s",
-        "frac": (achieved / alu_peak) if alu_peak else None,
-        "peak_source": "measured on this box by tools/pipe_peak.cu (DPX VIADDMNMX/VIMNMX3 "
-                       "issue rate, all SMs); MEASURED_PEAKS.json has no integer figure",
+        "bound": "int_alu", "kernel": f"sab_wave_kernel<{method},int16x2>",
+        "achieved": achieved, "peak": int_peak, "unit": "T lane-instr/s",
+        "frac": (achieved / int_peak) if int_peak else None,
+        "peak_source": "measured on this box in this run by tools/pipe_peak.cu: VIADDMNMX/VIMNMX3.U16x2 "
+                       "rate (alu pipe) + IMAD rate (fma pipe), all SMs; MEASURED_PEAKS.json has no "
+                       "integer figure",
         "instr_per_cell_algorithmic": INSTR_PER_CELL[method],
-        "instr_per_cell_issued": EXEC_INSTR_PER_CELL[method],
+        "alu_pipe": {"dpx_per_cell_issued": ALU_INSTR_PER_CELL[method], "achieved": alu_issued,
+                     "peak": dpx_peak, "frac": (alu_issued / dpx_peak) if dpx_peak else None,
+                     "unit": "T lane-instr/s"},
         "gcups_kernel_per_gpu": cells_per_s_gpu / 1e9,
+        "gcups_bound_per_gpu": (int_peak / INSTR_PER_CELL[method] * 1e3) if int_peak else None,
+        "launches_per_step": launches_value_leg / args.steps,
         "pipe_peaks_T_lane_instr_s": peaks,
         "traffic": traffic,
         "hbm": {"algorithmic_bytes_per_step": alg_bytes,
