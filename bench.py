@@ -114,11 +114,15 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
-def workload(config: str, n_gpus: int, n_override: int | None):
+def workload(config: str, n_gpus: int, n_override: int | None, method: str | None = None):
     from sequencealigner_b200 import AlignConfig, synth
     base = synth.CONFIGS[config]
     n = n_override or int(round(base["n"] * np.sqrt(n_gpus)))
     store, c = synth.make(config, n=n)
+    if method and method != c["method"]:  # informational runs: same sequences, other recurrence
+        c = {k: v for k, v in c.items() if k not in ("gap_pen", "gap_open", "gap_ext")}
+        c["method"] = method
+        c.update({"gap_pen": 4} if method == "nw" else {"gap_open": 10, "gap_ext": 1})
     cfg = AlignConfig(c["method"], c["matrix"], gap_pen=c.get("gap_pen"),
                       gap_open=c.get("gap_open"), gap_ext=c.get("gap_ext"))
     desc = {"workload": f"{config}: synthetic {'DNA' if c['alphabet'] == 'ACGT' else 'protein'} "
@@ -179,7 +183,7 @@ def run_reference_arm(args):
     rank, _, world = dist_env()
     if rank != 0:
         return 0
-    store, cfg, c, desc = workload(args.config, args.gpus, args.n)
+    store, cfg, c, desc = workload(args.config, args.gpus, args.n, args.method)
     per_step = max(4.0, min(20.0, 150.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
         cpu_reference_sample(store, c, target_s=per_step)
@@ -242,7 +246,7 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_gpus = world
 
-    store, cfg, c, desc = workload(args.config, n_gpus, args.n)
+    store, cfg, c, desc = workload(args.config, n_gpus, args.n, args.method)
     desc["parallelism"] = f"row-strip shards x{n_gpus}, no collective"
     desc["l2_flush"] = "512 MiB device memset between timed steps"
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
@@ -392,6 +396,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5"])
     ap.add_argument("--n", type=int, default=None, help="override the sequence count")
+    ap.add_argument("--method", default=None, choices=["nw", "ga", "sw"],
+                    help="override the config's alignment method (informational runs)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--flags", type=int, default=0, help="sab_config.flags (tuning / A-B runs)")
     ap.add_argument("--panel", type=int, default=0, help="sab_config.panel (0 = auto)")

@@ -26,10 +26,12 @@
  *        <- filter() decisions               src/bio/filter.c:14-62 (sequential -T 1 semantics)
  *   sab_matrix_lookup
  *        <- parse_matrix                     src/bio/matrices.c:44-57
+ *   sab_h5_write
+ *        <- flush_hdf5                       src/io/format/hdf5.c:14-202
  *
  * The reference-signature shim on top of this ABI (`bool cuda_align(struct input,
  * struct output)`, `bool cuda_memory(size_t)`, src/interface/seqalign_cuda.h:7-9)
- * is in sequencealigner_b200/csrc/seqalign_shim.cpp; INTEGRATION.md shows how a
+ * is in integration/seqalign_shim.c; INTEGRATION.md shows how a
  * reference maintainer links it.
  *
  * There is NO CPU fallback: every compute entry point fails with
@@ -188,6 +190,24 @@ const char *sab_matrix_name(int index);
 /* Fills SEQ_LUT / SUB_MAT for table `name` (case-insensitive, src/bio/matrices.c:47).
  * Returns SAB_OK or SAB_ERR_ARG. */
 int sab_matrix_lookup(const char *name, int32_t seq_lut[128], int32_t sub_mat[24 * 24]);
+
+/*
+ * Output format after the path (host only, no device needed): writes the HDF5 file of
+ * flush_hdf5() (src/io/format/hdf5.c:14-202) -- /sequences = dim variable-length C strings,
+ * /similarity_matrix = [dim,dim] int32 LE, contiguous when dim <= 256, else chunked
+ * (sab_h5_chunk_dim) with deflate level `compression` (0..9, 0 = none) -- without libhdf5.
+ * `matrix` is in either layout sab_align fills; a triangular one is expanded to the full
+ * symmetric matrix (diagonal 0) chunk by chunk.  `progress` gets (chunk rows done, total).
+ */
+typedef void (*sab_h5_progress_fn)(int64_t done, int64_t total, void *user);
+int sab_h5_write(const char *path, const char *const *seqs, size_t dim, const int32_t *matrix,
+		 int triangular, unsigned compression, sab_h5_progress_fn progress, void *user);
+/* Same with an explicit chunk edge (0 = contiguous, < 0 = the reference's rule). */
+int sab_h5_write_chunked(const char *path, const char *const *seqs, size_t dim, const int32_t *matrix,
+			 int triangular, unsigned compression, int chunk_dim,
+			 sab_h5_progress_fn progress, void *user);
+/* Chunk edge the reference's rule evaluates to (hdf5.c:68-84); 0 = contiguous. */
+int sab_h5_chunk_dim(size_t dim);
 
 #ifdef __cplusplus
 }

@@ -14,7 +14,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libseqalign_b200.so"
 PIPE_LIB = PKG / "libsab_pipepeak.so"
-SOURCES = ["sab_capi.cu", "sab_filter.cu", "sab_tables.cpp"]
+SOURCES = ["sab_capi.cu", "sab_filter.cu", "sab_tables.cpp", "sab_h5.cpp"]
 HEADERS = ["sab_kernels.cuh", "sab_wave.cuh", "sab_internal.h", "submat_tables.inc", "../../include/seqalign_b200.h"]
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
@@ -40,7 +40,7 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
     srcs = [CSRC / s for s in SOURCES if (CSRC / s).exists()]
     deps = srcs + [CSRC / h for h in HEADERS]
     if force or _stale(LIB, deps):
-        cmd = [nvcc(), *NVCC_FLAGS, "-o", str(LIB), *map(str, srcs)]
+        cmd = [nvcc(), *NVCC_FLAGS, "-o", str(LIB), *map(str, srcs), "-lz"]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         subprocess.run(cmd, check=True, cwd=str(CSRC))

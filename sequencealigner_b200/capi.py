@@ -74,6 +74,11 @@ SYMBOLS = {
     "sab_matrix_count": (C.c_int, []),
     "sab_matrix_name": (C.c_char_p, [C.c_int]),
     "sab_matrix_lookup": (C.c_int, [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "sab_h5_write": (C.c_int, [C.c_char_p, C.POINTER(C.c_char_p), C.c_size_t, C.c_void_p, C.c_int,
+                               C.c_uint, C.c_void_p, C.c_void_p]),
+    "sab_h5_write_chunked": (C.c_int, [C.c_char_p, C.POINTER(C.c_char_p), C.c_size_t, C.c_void_p,
+                                       C.c_int, C.c_uint, C.c_int, C.c_void_p, C.c_void_p]),
+    "sab_h5_chunk_dim": (C.c_int, [C.c_size_t]),
 }
 
 _lib = None

@@ -1,18 +1,18 @@
 // sab_wave.cuh -- systolic strip pipeline: the sm_100a kernel of the all-vs-all DP fill.
 //
 // Decomposition
-//   * lane = QUERY sequence (DP rows, streamed 4 letters per step from the lane-interleaved
+//   * lane = QUERY sequence (DP rows, streamed 8 letters per step from the lane-interleaved
 //     `rowpack`), block = 32 queries x a chunk of SUBJECT PAIRS (DP columns): the two
 //     subjects of a pair sit in the low/high int16 halves of every register, so each DPX
 //     instruction updates two cells.
-//   * The 4 warps of a block work on the SAME 32 queries and on 4 CONSECUTIVE 32-column
-//     strips of the stream of strips of the item's subject pairs:
+//   * The 4 warps of a block work on the SAME 32 queries and on 4 CONSECUTIVE K-column
+//     strips (K = 32 or 16) of the stream of strips of the item's subject pairs:
 //            step tau:   warp j computes row group (tau - j) mod G of its strip
-//     so warp j+1 is always one row group (4 rows) behind warp j, and the strip boundary
-//     column (V, X per row) travels warp j -> warp j+1 through an 8 KB shared-memory
+//     so warp j+1 is always one row group (8 rows) behind warp j, and the strip boundary
+//     column (V, X per row) travels warp j -> warp j+1 through a 12 KB shared-memory
 //     exchange buffer (the role the north star gives to __shfl_sync; lanes cannot be used
 //     for it because the conflict-free profile read needs all lanes of a warp on the same
-//     DP column).  Only the wrap-around warp 3 -> warp 0 (every 128 columns) goes through a
+//     DP column).  Only the wrap-around warp 3 -> warp 0 (every 4K columns) goes through a
 //     per-block global buffer small enough to stay in L2.  The stream never drains inside
 //     an item: a warp that finishes a strip starts the strip four positions further on.
 //   * Each strip's substitution scores are expanded once into a shared-memory PAIR PROFILE
@@ -29,12 +29,13 @@
 //         (Y floored at 0)    M = max3(Vdiag + (S - o), X, Y)   V = M + o           3.5 alu 3 fma
 //   NW/GA borders become constants (0 resp. o-e) and the score is V + g|e * (Lq + Ls).
 //   SW keeps the unskewed form because its zero floor would turn into a per-cell value.
-//   A 4-row group is issued in ANTI-DIAGONAL order (row k works on column t-k at time t):
-//   the 2-3 instruction dependency chain of a cell is interleaved with three independent
-//   ones, which is what lets 3 resident warps per scheduler keep the alu pipe busy
-//   (profiles/r1_ncu_wave_v1.md shows the serial order stalling at 65 % alu).
+//   An 8-row group is issued in ANTI-DIAGONAL order (row k works on column t-k at time t):
+//   the 2-3 instruction dependency chain of a cell is interleaved with seven independent
+//   ones, which is what lets 4-5 resident warps per scheduler keep the alu pipe busy
+//   (profiles/r1_ncu_wave_v1.md shows the serial order stalling at 65 % alu, r1_ncu_wave_v4.md
+//   the current 78 %).
 //
-// One __syncthreads per step (4 rows x 32 columns x 2 cells per thread).
+// One __syncthreads per step (8 rows x K columns x 2 cells per thread).
 #pragma once
 
 #include "sab_kernels.cuh"
@@ -117,7 +118,7 @@ __device__ __forceinline__ uint32_t cell(const CellK<METHOD, PACKED> &k, uint32_
 }
 
 // K = DP columns a warp holds in registers (strip width): 32 for long subjects, 16 for short
-// ones (less column padding, 6 resident blocks per SM instead of 4).
+// ones (less column padding, 5 resident blocks per SM instead of 4).
 template <int METHOD, bool PACKED, int K, int MINB>
 __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const TileParams p)
 {

@@ -58,30 +58,73 @@ def test_dropin_without_device_fails_loudly_instead_of_falling_back():
     assert p.returncode != 0 and not (Path(td) / "o.bin").exists()
 
 
-@pytest.mark.gpu
-@pytest.mark.parametrize("name", golden_cases())
-def test_dropin_matches_reference_cpu_build(name):
-    from oracle import oracle
+def run_dropin(fasta, cli, extra=()):
+    """Runs the drop-in CLI, returns (sequences, full matrix, stdout) read back from its HDF5."""
+    import h5min
+    out = Path(fasta).with_suffix(".h5")
+    cmd = [str(BIN), "-i", str(fasta), "-o", str(out), *cli, "-F", "-P", *extra]
+    p = subprocess.run(cmd, capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout + p.stderr
+    seqs, mat, info = h5min.read_similarity_file(out)
+    return seqs, mat, p.stdout
+
+
+def golden_full(g):
+    m = g["matrix"]
+    if not g["triangular"]:
+        return m
+    n = len(g["kept"])
+    full = np.zeros((n, n), dtype=np.int32)
+    full[np.tril_indices(n, -1)] = m
+    return full + full.T
+
+
+def write_fasta(td, seqs):
+    fa = Path(td) / "in.fasta"
+    fa.write_bytes(b"".join(b">s%d\n%s\n" % (k, s) for k, s in enumerate(seqs)))
+    return fa
+
+
+@pytest.mark.parametrize("name", ["protein_ga_blosum62_s10e1", "filter09_ga_blosum62",
+                                  "dna_sw_nuc44_s10e1"])
+def test_dropin_cli_and_hdf5_writer_on_the_reference_cpu_path(name):
+    """No GPU needed: with -C the reference's own CPU align() fills the matrix, so this pins the
+    rest of the drop-in -- CLI, filter, output_load and the library's HDF5 writer -- to the
+    golden output of the reference's CPU build."""
     ensure_built()
     g = load_golden(name)
     with tempfile.TemporaryDirectory() as td:
-        fa = Path(td) / "in.fasta"
-        fa.write_bytes(b"".join(b">s%d\n%s\n" % (k, s) for k, s in enumerate(g["seqs"])))
-        res = oracle.run_reference(fa, g["args"], threads=1, binary=BIN)
-    assert res["triangular"] == g["triangular"]
-    assert res["seqs"] == g["kept"]
-    assert np.array_equal(res["matrix"], g["matrix"])
+        seqs, mat, _ = run_dropin(write_fasta(td, g["seqs"]), g["args"], ["-C", "-T", "1", "-z", "4"])
+    assert seqs == g["kept"]
+    assert np.array_equal(mat, golden_full(g))
 
 
 @pytest.mark.gpu
-def test_dropin_no_write_and_benchmark_readout():
-    from oracle import oracle
-    from sequencealigner_b200 import synth
+@pytest.mark.parametrize("name", golden_cases())
+def test_dropin_matches_reference_cpu_build(name):
     ensure_built()
-    store, c = synth.make("c2", n=400)
+    g = load_golden(name)
+    with tempfile.TemporaryDirectory() as td:
+        seqs, mat, out = run_dropin(write_fasta(td, g["seqs"]), g["args"], ["-T", "1"])
+    assert "CUDA: Enabled (libseqalign_b200" in out
+    assert seqs == g["kept"]
+    assert np.array_equal(mat, golden_full(g))
+
+
+@pytest.mark.gpu
+def test_dropin_chunked_compressed_output_and_benchmark_readout(oracle_mod):
+    from sequencealigner_b200 import AlignConfig, synth
+    ensure_built()
+    store, c = synth.make("c2", n=600)
+    cfg = AlignConfig(c["method"], c["matrix"], gap_open=c["gap_open"], gap_ext=c["gap_ext"])
+    want, _ = oracle_mod.align_all(cfg.resolve(), store, triangular=False)
     with tempfile.TemporaryDirectory() as td:
         fa = Path(td) / "in.fasta"
         store.to_fasta(fa)
-        res = oracle.run_reference(fa, oracle.ref_args(**c), threads=0, write=False, bench=True,
-                                   binary=BIN)
-    assert res["align_seconds"] is not None and "Alignments per second" in res["stdout"]
+        seqs, mat, out = run_dropin(fa, oracle_mod.ref_args(**c), ["-z", "3", "-B", "-T", "0"])
+        p = subprocess.run([str(BIN), "-i", str(fa), *oracle_mod.ref_args(**c), "-F", "-P", "-W",
+                            "-B"], capture_output=True, text=True)
+    assert seqs == [store.sequence(k) for k in range(store.num)]
+    assert np.array_equal(mat, want)
+    assert "Alignments per second" in out
+    assert p.returncode == 0 and "Alignments per second" in p.stdout  # -W: no output file

@@ -217,3 +217,38 @@ def test_full_size_properties_c2_slice():
     again, _ = gpu_scores(AlignConfig("ga", "blosum62", gap_open=10, gap_ext=1), store, panel=384)
     assert int(again.astype(np.int64).sum()) == int(ga.astype(np.int64).sum())
     assert np.array_equal(again, ga)
+
+
+@pytest.mark.parametrize("config,n", [("c2", 10000), ("c3", 20000), ("c4", 30000), ("c5", 3000)])
+def test_baseline_sizes_sampled_pairs_and_checksums(oracle_mod, config, n):
+    """BASELINE.json workloads at (or near) full size: the whole matrix is computed on the
+    GPU; 3000 uniformly drawn pairs plus every pair of 24 whole rows are re-scored by the
+    CPU oracle, and the packed-triangular result must equal the full-layout result."""
+    store, c = synth.make(config, n=n)
+    cfg = AlignConfig(c["method"], c["matrix"], gap_pen=c.get("gap_pen"),
+                      gap_open=c.get("gap_open"), gap_ext=c.get("gap_ext"))
+    r = cfg.resolve()
+    with Aligner(cfg) as al:
+        al.upload(store)
+        tri = al.align(triangular=True)
+        st = al.stats()
+    assert st["pairs"] == store.pairs() and st["cells"] == store.cells()
+    rng = np.random.default_rng(11)
+    js = rng.integers(1, n, size=3000)
+    is_ = (rng.random(3000) * js).astype(np.int64)
+    for i, j in zip(is_.tolist(), js.tolist()):
+        want = oracle_mod.pair(r, store.sequence(j), store.sequence(i))
+        assert tri[j * (j - 1) // 2 + i] == want, (i, j)
+    # whole rows through the oracle's own all-vs-all driver (columns j of align(), align.c:21-72)
+    rows = sorted(set(rng.integers(1, min(n, 2500), size=24).tolist()) | {1})
+    for j in rows:
+        want, _ = oracle_mod.align_all(r, store.head(j + 1), first_j=j, last_j=j + 1)
+        lo = j * (j - 1) // 2
+        assert np.array_equal(tri[lo:lo + j], want[lo:lo + j]), j
+    if n <= 10000:
+        with Aligner(cfg) as al:
+            al.upload(store)
+            full = al.align(triangular=False)
+        iu = np.tril_indices(n, -1)
+        assert np.array_equal(full[iu], tri) and (np.diag(full) == 0).all()
+        assert np.array_equal(full, full.T)
