@@ -175,6 +175,25 @@ int sab_strip_info(const sab_ctx *ctx, int32_t strip, int32_t nshards, int32_t *
 int sab_get_stats(const sab_ctx *ctx, sab_stats *out);
 
 /*
+ * Every GPU of the box from one host process (what cuda_align needs: it is called once, on
+ * the main thread, src/main.c:31): one context and one host thread per device, each device
+ * holds a replica of the sequence set and fills its own shard of row strips of the caller's
+ * matrix -- sab_align_shard(k, ndev) on device k.  No collective.  ndev <= 0 = all devices.
+ * Stats: counts are summed over the devices, times are the slowest device's.  The progress
+ * callback is serialised and reports pairs over the whole job.
+ */
+typedef struct sab_multi sab_multi;
+int sab_multi_create(sab_multi **m, const sab_config *cfg, int32_t ndev);
+void sab_multi_destroy(sab_multi *m);
+const char *sab_multi_last_error(const sab_multi *m);
+int sab_multi_device_count(const sab_multi *m);
+int sab_multi_upload(sab_multi *m, const uint8_t *seqs, const sab_meta *meta, int32_t num,
+		     int32_t max);
+int sab_multi_align(sab_multi *m, int32_t *matrix, int triangular, sab_progress_fn progress,
+		    void *user);
+int sab_multi_get_stats(const sab_multi *m, sab_stats *out);
+
+/*
  * Redundancy filter decisions (src/bio/filter.c:14-62, the deterministic
  * sequential semantics): lost[j] = 1 iff some KEPT i<j has
  * (float)matches/(float)min(len_i,len_j) >= threshold over the common prefix.

@@ -133,14 +133,17 @@ bool cuda_align(struct input in, struct output out)
 	memcpy(cfg.seq_lut, SEQ_LUT, sizeof(SEQ_LUT));
 	memcpy(cfg.sub_mat, SUB_MAT, sizeof(SUB_MAT));
 
-	sab_ctx *ctx = nullptr;
+	/* every B200 of the box: one context + host thread per device, disjoint row strips */
+	sab_multi *m = nullptr;
 	bool ok = false;
-	if (sab_create(&ctx, &cfg) != SAB_OK) {
-		perr("%s", sab_last_error(ctx));
+	if (sab_multi_create(&m, &cfg, 0) != SAB_OK) {
+		perr("%s", sab_multi_last_error(m));
 		goto done;
 	}
-	if (sab_upload(ctx, in.seqs, (const sab_meta *)in.meta, in.num, in.max) != SAB_OK) {
-		perr("%s", sab_last_error(ctx));
+	pinfo("Using %d B200 device%s", sab_multi_device_count(m),
+	      sab_multi_device_count(m) == 1 ? "" : "s");
+	if (sab_multi_upload(m, in.seqs, (const sab_meta *)in.meta, in.num, in.max) != SAB_OK) {
+		perr("%s", sab_multi_last_error(m));
 		goto done;
 	}
 
@@ -148,24 +151,24 @@ bool cuda_align(struct input in, struct output out)
 	ppercent(0, "Aligning sequences");
 	bench_align_start();
 	/* out.matrix is NULL under -W (src/io/output.c:18): compute, copy nothing back */
-	const int rc = sab_align(ctx, out.matrix, out.triangular, on_progress, nullptr);
+	const int rc = sab_multi_align(m, out.matrix, out.triangular, on_progress, nullptr);
 	bench_align_end();
 	if (rc != SAB_OK) {
-		perr("%s", sab_last_error(ctx));
+		perr("%s", sab_multi_last_error(m));
 		goto done;
 	}
 	ppercent(100, "Aligning sequences");
 	bench_align_print();
 	{
 		sab_stats st;
-		if (sab_get_stats(ctx, &st) == SAB_OK)
+		if (sab_multi_get_stats(m, &st) == SAB_OK)
 			pverb("B200: %.1f GCUPS kernel, %lld kernel launches, %lld int32 re-runs",
 			      (double)st.cells / (st.kernel_ms * 1e6), (long long)st.launches,
 			      (long long)st.rerun_pairs);
 	}
 	ok = true;
 done:
-	sab_destroy(ctx);
+	sab_multi_destroy(m);
 	return ok;
 }
 

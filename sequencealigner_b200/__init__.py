@@ -2,8 +2,9 @@
 alignment (Needleman-Wunsch, Gotoh, Smith-Waterman), drop-in for that one path of
 jakovdev/SequenceAligner.  The product is libseqalign_b200.so (C ABI:
 include/seqalign_b200.h); this package is the Python host binding around it."""
-from .aligner import AlignConfig, Aligner, align_all, matrix_lookup, matrix_names  # noqa: F401
+from .aligner import (AlignConfig, Aligner, MultiAligner, align_all, matrix_lookup,  # noqa: F401
+                      matrix_names)
 from .seqstore import SeqStore, read_fasta  # noqa: F401
 
-__all__ = ["AlignConfig", "Aligner", "align_all", "matrix_lookup", "matrix_names", "SeqStore",
+__all__ = ["AlignConfig", "Aligner", "MultiAligner", "align_all", "matrix_lookup", "matrix_names", "SeqStore",
            "read_fasta"]

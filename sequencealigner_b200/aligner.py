@@ -204,6 +204,71 @@ class Aligner:
             pass
 
 
+class MultiAligner:
+    """All GPUs of the box from one process (sab_multi_*): what the reference-signature shim
+    drives.  ndev = 0 uses every usable device."""
+
+    def __init__(self, config: AlignConfig | dict, ndev: int = 0, panel: int = 0, flags: int = 0):
+        self._lib = capi.load()
+        r = config.resolve() if isinstance(config, AlignConfig) else dict(config)
+        cfg = capi.SabConfig()
+        cfg.method = int(r["method"])
+        cfg.gap_pen, cfg.gap_open, cfg.gap_ext = int(r["gap_pen"]), int(r["gap_open"]), int(r["gap_ext"])
+        cfg.seq_lut[:] = [int(v) for v in np.asarray(r["seq_lut"]).reshape(128)]
+        cfg.sub_mat[:] = [int(v) for v in np.asarray(r["sub_mat"]).reshape(576)]
+        cfg.panel, cfg.flags = panel, flags
+        self._m = C.c_void_p()
+        rc = self._lib.sab_multi_create(C.byref(self._m), C.byref(cfg), ndev)
+        if rc != capi.SAB_OK:
+            msg = self._lib.sab_multi_last_error(self._m).decode() if self._m else "sab_multi_create"
+            self.close()
+            raise capi.SabError(rc, msg)
+        self.ndev = self._lib.sab_multi_device_count(self._m)
+        self.num = 0
+
+    def _check(self, rc: int):
+        if rc != capi.SAB_OK:
+            raise capi.SabError(rc, self._lib.sab_multi_last_error(self._m).decode())
+
+    def upload(self, store: SeqStore) -> None:
+        seqs = np.ascontiguousarray(store.seqs, dtype=np.uint8)
+        meta = np.ascontiguousarray(store.meta)
+        self._check(self._lib.sab_multi_upload(self._m, seqs.ctypes.data,
+                                               meta.ctypes.data_as(C.POINTER(capi.SabMeta)),
+                                               store.num, store.max))
+        self.num = store.num
+
+    def align(self, triangular: bool = True, out: np.ndarray | None = None, write: bool = True,
+              progress=None) -> np.ndarray | None:
+        n = self.num
+        if write:
+            if out is None:
+                out = np.zeros(n * (n - 1) // 2 if triangular else (n, n), dtype=np.int32)
+            ptr = out.ctypes.data
+        else:
+            out, ptr = None, None
+        cb = capi.PROGRESS_FN(progress) if progress else None
+        self._check(self._lib.sab_multi_align(self._m, ptr, int(triangular),
+                                              C.cast(cb, C.c_void_p) if cb else None, None))
+        return out
+
+    def stats(self) -> dict:
+        st = capi.SabStats()
+        self._check(self._lib.sab_multi_get_stats(self._m, C.byref(st)))
+        return st.as_dict()
+
+    def close(self) -> None:
+        if self._m:
+            self._lib.sab_multi_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
 def align_all(store: SeqStore, config: AlignConfig, triangular: bool = True, device: int = 0,
               **kw) -> tuple[np.ndarray, SeqStore]:
     """input_load's filter step + cuda_align in one call (main.c:22-32): returns the

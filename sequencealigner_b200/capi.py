@@ -69,6 +69,13 @@ SYMBOLS = {
                                   C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                   C.POINTER(C.c_int32)]),
     "sab_get_stats": (C.c_int, [C.c_void_p, C.POINTER(SabStats)]),
+    "sab_multi_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(SabConfig), C.c_int32]),
+    "sab_multi_destroy": (None, [C.c_void_p]),
+    "sab_multi_last_error": (C.c_char_p, [C.c_void_p]),
+    "sab_multi_device_count": (C.c_int, [C.c_void_p]),
+    "sab_multi_upload": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(SabMeta), C.c_int32, C.c_int32]),
+    "sab_multi_align": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "sab_multi_get_stats": (C.c_int, [C.c_void_p, C.POINTER(SabStats)]),
     "sab_filter": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(SabMeta), C.c_int32, C.c_float,
                              C.c_void_p]),
     "sab_matrix_count": (C.c_int, []),

@@ -1051,3 +1051,172 @@ int sab_get_stats(const sab_ctx *ctx, sab_stats *out)
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// All GPUs of the box from ONE host process: one context + one host thread per device,
+// every device holds a replica of the sequence set and computes its own shard of row
+// strips straight into the caller's matrix (disjoint rows -> no locking, no collective).
+// This is what the reference-signature shim (integration/seqalign_shim.c) drives.
+// ---------------------------------------------------------------------------------------
+#include <mutex>
+
+struct sab_multi {
+	std::vector<sab_ctx *> ctx;
+	std::string err;
+	sab_stats stats{};
+	// progress aggregation
+	std::mutex mu;
+	std::vector<int64_t> done;
+	int64_t total = 0;
+	sab_progress_fn progress = nullptr;
+	void *user = nullptr;
+};
+
+namespace {
+
+struct MultiSlot {
+	sab_multi *m;
+	int k;
+};
+
+void multi_progress(int64_t done, int64_t, void *user)
+{
+	MultiSlot *s = static_cast<MultiSlot *>(user);
+	sab_multi *m = s->m;
+	std::lock_guard<std::mutex> lock(m->mu);
+	m->done[s->k] = done;
+	int64_t sum = 0;
+	for (int64_t d : m->done)
+		sum += d;
+	if (m->progress)
+		m->progress(sum, m->total, m->user);
+}
+
+template <typename F> int multi_run(sab_multi *m, F fn)
+{
+	const int n = (int)m->ctx.size();
+	std::vector<int> rc(n, SAB_OK);
+	std::vector<std::thread> th;
+	for (int k = 0; k < n; k++)
+		th.emplace_back([&, k]() { rc[k] = fn(k); });
+	for (auto &t : th)
+		t.join();
+	for (int k = 0; k < n; k++)
+		if (rc[k] != SAB_OK) {
+			m->err = "device " + std::to_string(k) + ": " + sab_last_error(m->ctx[k]);
+			return rc[k];
+		}
+	return SAB_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int sab_multi_create(sab_multi **out, const sab_config *cfg, int32_t ndev)
+{
+	if (!out || !cfg)
+		return SAB_ERR_ARG;
+	*out = nullptr;
+	sab_multi *m = new (std::nothrow) sab_multi;
+	if (!m)
+		return SAB_ERR_NOMEM;
+	*out = m;
+	const int have = sab_device_count();
+	if (ndev <= 0)
+		ndev = have;
+	if (have == 0 || ndev > have) {
+		m->err = have ? "more devices requested than present" :
+				"no CUDA device (this library has no CPU fallback)";
+		return SAB_ERR_NODEVICE;
+	}
+	for (int k = 0; k < ndev; k++) {
+		sab_config c = *cfg;
+		c.device = k;
+		c.shards_hint = ndev;
+		sab_ctx *ctx = nullptr;
+		const int rc = sab_create(&ctx, &c);
+		m->ctx.push_back(ctx);
+		if (rc != SAB_OK) {
+			m->err = "device " + std::to_string(k) + ": " + sab_last_error(ctx);
+			return rc;
+		}
+	}
+	m->done.assign(ndev, 0);
+	return SAB_OK;
+}
+
+void sab_multi_destroy(sab_multi *m)
+{
+	if (!m)
+		return;
+	for (sab_ctx *c : m->ctx)
+		sab_destroy(c);
+	delete m;
+}
+
+const char *sab_multi_last_error(const sab_multi *m)
+{
+	return m ? m->err.c_str() : "null context";
+}
+
+int sab_multi_device_count(const sab_multi *m)
+{
+	return m ? (int)m->ctx.size() : 0;
+}
+
+int sab_multi_upload(sab_multi *m, const uint8_t *seqs, const sab_meta *meta, int32_t num, int32_t max)
+{
+	if (!m || m->ctx.empty())
+		return SAB_ERR_ARG;
+	return multi_run(m, [&](int k) { return sab_upload(m->ctx[k], seqs, meta, num, max); });
+}
+
+int sab_multi_align(sab_multi *m, int32_t *matrix, int triangular, sab_progress_fn progress, void *user)
+{
+	if (!m || m->ctx.empty())
+		return SAB_ERR_ARG;
+	const int n = (int)m->ctx.size();
+	m->progress = progress;
+	m->user = user;
+	std::fill(m->done.begin(), m->done.end(), 0);
+	m->total = m->ctx[0]->uploaded ? tri(m->ctx[0]->num) : 0;
+	std::vector<MultiSlot> slots(n);
+	for (int k = 0; k < n; k++)
+		slots[k] = { m, k };
+	const double t0 = now_ms();
+	const int rc = multi_run(m, [&](int k) {
+		return sab_align_shard(m->ctx[k], k, n, matrix, triangular, multi_progress, &slots[k]);
+	});
+	if (rc != SAB_OK)
+		return rc;
+	sab_stats S{};
+	for (int k = 0; k < n; k++) { // counts add up; times are the slowest device's
+		const sab_stats &s = m->ctx[k]->stats;
+		S.kernel_ms = std::max(S.kernel_ms, s.kernel_ms);
+		S.busy_ms = std::max(S.busy_ms, s.busy_ms);
+		S.device_ms = std::max(S.device_ms, s.device_ms);
+		S.upload_ms = std::max(S.upload_ms, s.upload_ms);
+		S.pairs += s.pairs;
+		S.cells += s.cells;
+		S.rerun_pairs += s.rerun_pairs;
+		S.launches += s.launches;
+		S.tiles += s.tiles;
+		S.tiles_int32 += s.tiles_int32;
+		S.h2d_bytes += s.h2d_bytes;
+		S.d2h_bytes += s.d2h_bytes;
+	}
+	S.total_ms = now_ms() - t0;
+	m->stats = S;
+	return SAB_OK;
+}
+
+int sab_multi_get_stats(const sab_multi *m, sab_stats *out)
+{
+	if (!m || !out)
+		return SAB_ERR_ARG;
+	*out = m->stats;
+	return SAB_OK;
+}
+
+} // extern "C"

@@ -252,3 +252,24 @@ def test_baseline_sizes_sampled_pairs_and_checksums(oracle_mod, config, n):
         iu = np.tril_indices(n, -1)
         assert np.array_equal(full[iu], tri) and (np.diag(full) == 0).all()
         assert np.array_equal(full, full.T)
+
+
+def test_multi_device_single_process_equals_single_device(oracle_mod):
+    """sab_multi_*: all devices of the box from one process (1 device on the test box is fine:
+    the same code path, one shard)."""
+    from sequencealigner_b200 import MultiAligner
+    store, c = synth.make("c5", n=1200)
+    cfg = AlignConfig("sw", "blosum62", gap_open=10, gap_ext=1)
+    want, _ = oracle_mod.align_all(cfg.resolve(), store, triangular=True)
+    seen = []
+    with MultiAligner(cfg, panel=128) as ma:
+        assert ma.ndev >= 1
+        ma.upload(store)
+        got = ma.align(triangular=True, progress=lambda d, t, u: seen.append((d, t)))
+        st = ma.stats()
+        full = ma.align(triangular=False)
+    assert np.array_equal(got, want)
+    assert st["pairs"] == store.pairs() and st["cells"] == store.cells()
+    assert seen and seen[-1] == (store.pairs(), store.pairs())
+    assert all(a[0] <= b[0] for a, b in zip(seen, seen[1:]))
+    assert np.array_equal(full[np.tril_indices(store.num, -1)], want)
