@@ -179,6 +179,36 @@ def cpu_reference_sample(store, c, target_s: float = 15.0):
                       f"alignment time, threads=all)", "_cells": cells, "_secs": secs, "_m": m}
 
 
+def cli_end_to_end(store, c, binary, threads=0, extra=()):
+    """End-to-end pairs/s of a `seqalign` CLI build (BASELINE.json: "end-to-end pairs/sec" =
+    pairs / wall time of the whole run: FASTA parse, filter, alignment, HDF5 write)."""
+    import re
+    import shutil
+    td = tempfile.mkdtemp(prefix="sab_cli_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    try:
+        fa = Path(td) / "in.fasta"
+        store.to_fasta(fa)
+        from oracle import oracle  # only for the flag spelling (ref_args); nothing is computed there
+        out = Path(td) / "out.h5"
+        cmd = [str(binary), "-i", str(fa), "-o", str(out), *oracle.ref_args(**c), "-F", "-P", "-B",
+               "-T", str(threads), *extra]
+        t0 = time.perf_counter()
+        p = subprocess.run(cmd, capture_output=True, text=True)
+        wall = time.perf_counter() - t0
+        if p.returncode != 0:
+            return {"error": (p.stdout + p.stderr)[-300:]}
+        m = re.search(r"Alignment:\s*([0-9.]+)\s*sec", p.stdout)
+        dev = re.search(r"Using (\d+) B200", p.stdout)
+        return {"pairs_per_s": store.pairs() / wall, "wall_s": wall,
+                "align_s": float(m.group(1)) if m else None,
+                "output_bytes": out.stat().st_size if out.exists() else 0,
+                "devices": int(dev.group(1)) if dev else 0,
+                "what": "integration/_build/seqalign_b200 (unmodified reference host + this "
+                        "library): FASTA parse + alignment + HDF5 write, wall clock"}
+    finally:
+        shutil.rmtree(td, ignore_errors=True)
+
+
 def run_reference_arm(args):
     rank, _, world = dist_env()
     if rank != 0:
@@ -364,6 +394,11 @@ def run_ours(args):
                 "note": "non-binding"},
     }
 
+    cli = None
+    dropin = ROOT / "integration" / "_build" / "seqalign_b200"
+    if n_gpus == 1 and not args.no_cli and dropin.exists():
+        cli = cli_end_to_end(store, c, dropin)
+
     cpu = None
     if n_gpus == 1 and not args.no_cpu:
         cpu = cpu_reference_sample(store, c, target_s=args.cpu_seconds)
@@ -381,6 +416,7 @@ def run_ours(args):
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "checksum": checksum},
         "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+        "cli_end_to_end": cli,
     }
     print(json.dumps(out), flush=True)
     if world > 1:
@@ -399,6 +435,7 @@ def main():
     ap.add_argument("--method", default=None, choices=["nw", "ga", "sw"],
                     help="override the config's alignment method (informational runs)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cli", action="store_true", help="skip the drop-in CLI end-to-end leg")
     ap.add_argument("--flags", type=int, default=0, help="sab_config.flags (tuning / A-B runs)")
     ap.add_argument("--panel", type=int, default=0, help="sab_config.panel (0 = auto)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)

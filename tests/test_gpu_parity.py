@@ -273,3 +273,20 @@ def test_multi_device_single_process_equals_single_device(oracle_mod):
     assert seen and seen[-1] == (store.pairs(), store.pairs())
     assert all(a[0] <= b[0] for a, b in zip(seen, seen[1:]))
     assert np.array_equal(full[np.tril_indices(store.num, -1)], want)
+
+
+@pytest.mark.parametrize("method,kw", METHODS)
+def test_long_sequences_beyond_the_reference_cuda_cap(oracle_mod, method, kw):
+    """The reference's CUDA backend refuses lengths > 1023 (seqalign_cuda.c:102-105); its CPU
+    path does not.  Lengths up to 6000: many wrap-arounds of the strip pipeline, int32 routing
+    for NW (the all-gap border leaves int16), int16 for SW."""
+    rng = np.random.default_rng(17)
+    lens = np.concatenate([rng.integers(1500, 6001, size=20), rng.integers(1, 200, size=12)])
+    rng.shuffle(lens)
+    store = SeqStore.from_codes(rng.integers(0, 20, size=int(lens.sum())), lens, synth.PROTEIN20)
+    cfg = AlignConfig(method, "blosum62", **kw)
+    want, _ = oracle_mod.align_all(cfg.resolve(), store, triangular=True)
+    got, st = gpu_scores(cfg, store, triangular=True)
+    assert np.array_equal(got, want)
+    if method == "nw":
+        assert st["tiles_int32"] > 0

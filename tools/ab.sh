@@ -3,7 +3,7 @@
 # usage: tools/ab.sh "<flags list>" [extra bench args]
 FL="$1"; shift
 for f in $FL; do
-  timeout 600 python bench.py --no-cpu --steps 2 --warmup 1 --flags $f "$@" 2>/dev/null | python -c "
+  timeout 600 python bench.py --no-cpu --no-cli --steps 2 --warmup 1 --flags $f "$@" 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read().strip().splitlines()[-1])
 r=d['roofline']
