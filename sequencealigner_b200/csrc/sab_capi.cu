@@ -120,7 +120,13 @@ typedef void (*tile_kernel_t)(const TileParams);
 
 // Kernel variants: [narrow] strip width 32 (4 resident blocks/SM) or 16 (5 blocks/SM).
 constexpr int kStripWide = 32, kStripNarrow = 16;
-constexpr int kMinbWide = 4, kMinbNarrow = 5;
+#ifndef SAB_MINB_WIDE
+#define SAB_MINB_WIDE 4
+#endif
+#ifndef SAB_MINB_NARROW
+#define SAB_MINB_NARROW 5
+#endif
+constexpr int kMinbWide = SAB_MINB_WIDE, kMinbNarrow = SAB_MINB_NARROW;
 
 template <int K, int MINB> tile_kernel_t pick_wave_kernel_t(int method, bool packed)
 {

@@ -97,6 +97,11 @@ template <> struct VOps<true> {
 	{
 		return imad_add(a, one, d);
 	}
+	// two per-lane signed addends for the DPX add-max ops (each wraps inside its own lane)
+	static __device__ __forceinline__ uint32_t lane2(int lo, int hi)
+	{
+		return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16);
+	}
 	// per-lane addend for the DPX add-max ops (wraps inside each lane)
 	static __device__ __forceinline__ uint32_t lane(int v)
 	{
@@ -122,6 +127,7 @@ template <> struct VOps<true> {
 template <> struct VOps<false> {
 	static __device__ __forceinline__ uint32_t delta(int v) { return (uint32_t)v; }
 	static __device__ __forceinline__ uint32_t delta2(int lo, int) { return (uint32_t)lo; }
+	static __device__ __forceinline__ uint32_t lane2(int lo, int) { return (uint32_t)lo; }
 	static __device__ __forceinline__ uint32_t addw(uint32_t a, uint32_t d, uint32_t one)
 	{
 		return imad_add(a, one, d);

@@ -42,6 +42,20 @@
 
 #include <type_traits>
 
+#ifndef SAB_ORDER
+#define SAB_ORDER 0
+#endif
+#if SAB_ORDER == 0 // anti-diagonal
+#define SAB_TT_END (K + NR - 1)
+#define SAB_CELL_COL const int c = tt - k;
+#elif SAB_ORDER == 1 // skewed by 2
+#define SAB_TT_END (K + 2 * (NR - 1))
+#define SAB_CELL_COL const int c = tt - 2 * k;
+#elif SAB_ORDER == 2 // row-major
+#define SAB_TT_END (K * NR)
+#define SAB_CELL_COL const int c = (tt / K == k) ? tt % K : -1;
+#endif
+
 namespace sab {
 
 constexpr int kWaveWarps = 4;
@@ -88,7 +102,7 @@ __device__ __forceinline__ uint32_t cell(const CellK<METHOD, PACKED> &k, uint32_
 {
 	using O = VOps<PACKED>;
 	const uint32_t tt = V;
-	const uint32_t d = O::addw(dg, s, k.one); // fma pipe
+	const uint32_t d = (METHOD == M_SW && PACKED) ? 0u : O::addw(dg, s, k.one); // fma pipe
 	uint32_t m;
 	if (METHOD == M_NW) {
 		m = O::max3(d, ml, tt);
@@ -102,14 +116,22 @@ __device__ __forceinline__ uint32_t cell(const CellK<METHOD, PACKED> &k, uint32_
 	} else {
 		uint32_t y;
 		if (PACKED) {
-			const uint32_t ye = O::addw(Yc, k.dE, k.one); // fma pipe
-			y = O::max3(ye, tt, k.ZERO);
+			// The zero floor sits on the diagonal term (M = max(0, Mdiag + S, X, Y); a negative
+			// X or Y can never win against it nor against a later M + o), so both gap adds and
+			// the score add ride inside DPX add-max ops: 4.5 alu + 1 fma per cell pair.  Measured
+			// (tools/cell_peak.cu) 4 % faster than 3.5 alu + 3 fma: an IMAD next to a saturated
+			// DPX stream costs ~0.8 clk, not 0.  `s` is in per-lane encoding here (O::lane2).
+			const uint32_t d2 = O::addmax(dg, s, k.ZERO);
+			y = O::addmax(Yc, k.lG, tt);
+			x = O::addmax(x, k.lG, ml);
+			m = O::max3(d2, x, y);
+			Yc = y;
 		} else {
 			y = (uint32_t)__viaddmax_s32_relu((int)Yc, k.gE, (int)tt);
+			Yc = y;
+			x = O::addmax(x, k.lG, ml);
+			m = O::max3(d, x, y);
 		}
-		x = O::addmax(x, k.lG, ml);
-		m = O::max3(d, x, y);
-		Yc = y;
 		ml = O::addw(m, k.dA, k.one); // fma pipe
 	}
 	dg = tt;
@@ -247,7 +269,7 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 				const int32_t *r1 = sm.ssub + a1 * kLetters;
 #pragma unroll 5
 				for (int q = 0; q < kLetters; q++)
-					dst[q] = O::delta2(r0[q], r1[q]);
+					dst[q] = METHOD == M_SW ? O::lane2(r0[q], r1[q]) : O::delta2(r0[q], r1[q]);
 			}
 		};
 
@@ -333,10 +355,10 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 						}
 						diag = b[NR - 1].x;
 #pragma unroll
-						for (int tt = 0; tt < K + NR - 1; tt++) {
+						for (int tt = 0; tt < SAB_TT_END; tt++) {
 #pragma unroll
 							for (int k = 0; k < NR; k++) {
-								const int c = tt - k;
+								SAB_CELL_COL
 								if (c < 0 || c >= K)
 									continue;
 								const uint32_t m = cell<METHOD, PACKED>(
