@@ -39,7 +39,7 @@ sys.path.insert(0, str(ROOT))
 # algorithmic integer lane-instructions per DP cell
 INSTR_PER_CELL = {"nw": 1.5, "ga": 3.0, "sw": 3.5}
 # DPX (alu-pipe) instructions the kernel issues per cell
-ALU_INSTR_PER_CELL = {"nw": 0.5, "ga": 1.5, "sw": 1.75}
+ALU_INSTR_PER_CELL = {"nw": 0.5, "ga": 1.5, "sw": 2.25}
 
 
 def dist_env():

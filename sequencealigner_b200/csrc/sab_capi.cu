@@ -624,6 +624,7 @@ struct Strip {
 	bool packed;
 	bool narrow; // 16-column register strips (short subjects)
 	int lq, ls; // longest query / subject
+	double mean_ls; // mean subject length (strip width and chunk size heuristics)
 };
 
 int ensure(sab_ctx *ctx, void **p, size_t *cap, size_t need, size_t elem)
@@ -666,6 +667,7 @@ void plan_strips(const sab_ctx *ctx, int nshards, std::vector<Strip> &strips, st
 		// strip width: padding a subject to 16 instead of 32 columns saves ~8 columns per
 		// subject, the narrow kernel costs ~4 % (profiles/r1_variants.md) -> narrow below ~160
 		const double mean_ls = (double)ctx->len_prefix[s.a0 + s.an] / (s.a0 + s.an);
+		s.mean_ls = mean_ls;
 		s.narrow = (ctx->cfg.flags & SAB_FLAG_STRIP16) ||
 			   (!(ctx->cfg.flags & SAB_FLAG_STRIP32) && mean_ls < 160.0);
 	}
@@ -837,7 +839,14 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		p.blk = b.blk;
 		p.tri0 = tri(st.a0);
 		p.blkT = (!triangular && matrix) ? b.blkT : nullptr;
-		p.chunk = packed ? 16 : 8;
+		// Work item = 32 queries x `chunk` subjects.  An item pays 3 steps of pipeline fill, so
+		// short subjects get more of them per item: aim at >= 24 rounds (4 strips each).
+		{
+			const int width = narrow ? kStripNarrow : kStripWide;
+			const int strips = std::max(1, (int)((st.mean_ls + width - 1) / width));
+			const int mult = std::min(8, std::max(1, (24 + 2 * strips - 1) / (2 * strips)));
+			p.chunk = (packed ? 16 : 8) * mult;
+		}
 		p.nsc = (a1 + p.chunk - 1) / p.chunk;
 		p.counter = b.counter;
 		p.bnd = b.bnd;
