@@ -263,6 +263,26 @@ def measure_pipe_peak(device: int):
     return out
 
 
+def measure_cell_ceiling(device: int, method: str, narrow: bool):
+    """TCUPS of the bare 8-row register block of the kernel (tools/cell_peak.cu): what this
+    instruction mix reaches on this GPU with no queue, strip boundaries or staging."""
+    import ctypes as C
+    from sequencealigner_b200.build import PIPE_LIB
+    if not PIPE_LIB.exists():
+        return None
+    lib = C.CDLL(str(PIPE_LIB))
+    if not hasattr(lib, "sab_cell_peak"):
+        return None
+    lib.sab_cell_peak.restype = C.c_int
+    lib.sab_cell_peak.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    t, clk = C.c_double(), C.c_double()
+    if lib.sab_cell_peak({"nw": 0, "ga": 1, "sw": 2}[method], int(narrow), device, C.byref(t), C.byref(clk)) != 0:
+        return None
+    return {"gcups": t.value * 1e3, "clk_per_cell_pair_per_smsp": clk.value,
+            "strip_columns": 16 if narrow else 32,
+            "source": "tools/cell_peak.cu measured in this run: the kernel's unrolled 8-row block alone"}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -393,6 +413,11 @@ def run_ours(args):
                 "peak_source": "MEASURED_PEAKS.json" if measured else "fallback",
                 "note": "non-binding"},
     }
+
+    ceiling = measure_cell_ceiling(local_rank, method, float(store.lengths.mean()) < 160.0)
+    if ceiling:
+        ceiling["kernel_frac_of_ceiling"] = cells_per_s_gpu / 1e9 / ceiling["gcups"]
+    roofline["code_shape_ceiling"] = ceiling
 
     cli = None
     dropin = ROOT / "integration" / "_build" / "seqalign_b200"

@@ -48,10 +48,13 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
 
 
 def build_pipe_peak(force: bool = False) -> Path:
-    """Integer-pipe peak microbenchmark (roofline denominator, bench.py only)."""
-    src = PKG.parent / "tools" / "pipe_peak.cu"
-    if force or _stale(PIPE_LIB, [src]):
-        subprocess.run([nvcc(), *NVCC_FLAGS, "-o", str(PIPE_LIB), str(src)], check=True)
+    """Measurement infrastructure for bench.py only: integer-pipe peaks (tools/pipe_peak.cu, the
+    roofline denominator) and the ceiling of the bare DP register block (tools/cell_peak.cu)."""
+    tools = PKG.parent / "tools"
+    srcs = [tools / "pipe_peak.cu", tools / "cell_peak.cu"]
+    if force or _stale(PIPE_LIB, srcs + [CSRC / "sab_wave.cuh", CSRC / "sab_kernels.cuh"]):
+        subprocess.run([nvcc(), *NVCC_FLAGS, "-DCELL_PEAK_LIB", "-I", str(CSRC), "-I", str(PKG.parent / "include"),
+                        "-o", str(PIPE_LIB), *map(str, srcs)], check=True)
     return PIPE_LIB
 
 

@@ -77,6 +77,7 @@ struct sab_ctx {
 	int32_t num = 0, max_len = 0, panel = 0;
 	std::vector<int32_t> slot_len, slot_orig;
 	std::vector<int64_t> len_prefix; // len_prefix[s] = sum of slot_len[0..s)
+	std::vector<int64_t> pad16_prefix, pad32_prefix; // same, lengths rounded up to 16 / 32 columns
 	std::vector<int32_t> panel_maxlen;
 	int32_t *d_slot_len = nullptr, *d_slot_orig = nullptr;
 	int64_t *d_col_off = nullptr, *d_grp_off = nullptr;
@@ -533,15 +534,21 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 		std::stable_sort(b, e, [&](int32_t x, int32_t y) { return meta[x].len < meta[y].len; });
 		panel_maxlen[p] = meta[*(e - 1)].len;
 	}
-	std::vector<int64_t> col_off(num), len_prefix(num + 1);
-	int64_t off = 0;
+	std::vector<int64_t> col_off(num), len_prefix(num + 1), pad16_prefix(num + 1), pad32_prefix(num + 1);
+	int64_t off = 0, off16 = 0, off32 = 0;
 	for (int32_t s = 0; s < num; s++) {
 		slot_len[s] = meta[slot_orig[s]].len;
 		col_off[s] = off;
 		len_prefix[s] = off;
+		pad16_prefix[s] = off16;
+		pad32_prefix[s] = off32;
 		off += slot_len[s];
+		off16 += (slot_len[s] + 15) / 16 * 16;
+		off32 += (slot_len[s] + 31) / 32 * 32;
 	}
 	len_prefix[num] = off;
+	pad16_prefix[num] = off16;
+	pad32_prefix[num] = off32;
 
 	// Subject layout: one byte per residue, index 0..23.
 	std::vector<uint8_t> col_bytes((size_t)letters + 16, 24);
@@ -605,6 +612,8 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 	ctx->slot_len.swap(slot_len);
 	ctx->slot_orig.swap(slot_orig);
 	ctx->len_prefix.swap(len_prefix);
+	ctx->pad16_prefix.swap(pad16_prefix);
+	ctx->pad32_prefix.swap(pad32_prefix);
 	ctx->panel_maxlen.swap(panel_maxlen);
 	ctx->uploaded = true;
 	ctx->stats.upload_ms = now_ms() - t0;
@@ -664,12 +673,16 @@ void plan_strips(const sab_ctx *ctx, int nshards, std::vector<Strip> &strips, st
 		const double ls_sum = (double)ctx->len_prefix[s.a0] + 0.5 * lq_sum;
 		s.cost = lq_sum * ls_sum;
 		s.packed = !force32 && (force16 || int16_safe(ctx, s.lq, s.ls));
-		// strip width: padding a subject to 16 instead of 32 columns saves ~8 columns per
-		// subject, the narrow kernel costs ~4 % (profiles/r1_variants.md) -> narrow below ~160
-		const double mean_ls = (double)ctx->len_prefix[s.a0 + s.an] / (s.a0 + s.an);
+		// Strip width: the subjects of this strip (every slot below its last query) padded to 16
+		// or to 32 DP columns.  A 16-column step carries the same bookkeeping as a 32-column one
+		// for half the cells: measured 5.5 % more time per padded column (C3, len 150: 6.11 vs
+		// 6.44 TCUPS at equal padding), so the narrow kernel must save more than that.
+		const int a1 = s.a0 + s.an;
+		const double mean_ls = (double)ctx->len_prefix[a1] / a1;
 		s.mean_ls = mean_ls;
+		const double cols16 = (double)ctx->pad16_prefix[a1], cols32 = (double)ctx->pad32_prefix[a1];
 		s.narrow = (ctx->cfg.flags & SAB_FLAG_STRIP16) ||
-			   (!(ctx->cfg.flags & SAB_FLAG_STRIP32) && mean_ls < 160.0);
+			   (!(ctx->cfg.flags & SAB_FLAG_STRIP32) && cols16 * 1.055 < cols32);
 	}
 	std::vector<double> cost(npanels);
 	for (int p = 0; p < npanels; p++)

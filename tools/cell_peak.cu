@@ -7,8 +7,9 @@
 // reach with this instruction mix and occupancy; the gap between the two is what the
 // pipeline plumbing costs.  Not part of the product path.
 //
-//   nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -I sequencealigner_b200/csrc \
-//        -I include -o tools/cell_peak tools/cell_peak.cu && tools/cell_peak
+//   nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -I sequencealigner_b200/csrc
+//        -I include -o tools/cell_peak tools/cell_peak.cu ; tools/cell_peak
+// With -DCELL_PEAK_LIB only sab_cell_peak() is built (bench.py, libsab_pipepeak.so).
 #include "sab_wave.cuh"
 
 #include <cstdio>
@@ -100,7 +101,8 @@ __global__ void __launch_bounds__(128, MINB) micro(uint32_t *out, int iters, int
 }
 
 template <int METHOD, int K, int MINB, bool LDS_ON, bool BAR, int NR = 8>
-static void run(const char *name, uint32_t *out, const uint32_t *letters, int sms, double mhz, int occ_cap = 0)
+static double run(const char *name, uint32_t *out, const uint32_t *letters, int sms, double mhz, int occ_cap = 0,
+		  double *clk_out = nullptr)
 {
 	const int iters = 20000 / (K / 16) * 8 / NR;
 	auto kern = micro<METHOD, K, MINB, LDS_ON, BAR, NR>;
@@ -130,11 +132,20 @@ static void run(const char *name, uint32_t *out, const uint32_t *letters, int sm
 	const double pairs_per_smsp = (double)occ * iters * (double)NR * K; // one warp per SMSP per block
 	const double clk = best * 1e-3 * mhz * 1e6 / pairs_per_smsp;
 	const double tcups = (double)blocks * 4 * iters * (double)NR * K * 64 / (best * 1e-3) / 1e12;
-	printf("%-34s blocks/SM %d  %.2f ms  %.2f clk/cell-pair/SMSP (at %.0f MHz)  %.2f TCUPS\n", name, occ,
-	       best, clk, mhz, tcups);
+	if (name)
+		printf("%-34s blocks/SM %d  %.2f ms  %.2f clk/cell-pair/SMSP (at %.0f MHz)  %.2f TCUPS\n", name,
+		       occ, best, clk, mhz, tcups);
 	cudaError_t e = cudaGetLastError();
-	if (e != cudaSuccess)
-		printf("  CUDA error: %s\n", cudaGetErrorString(e));
+	if (e != cudaSuccess) {
+		if (name)
+			printf("  CUDA error: %s\n", cudaGetErrorString(e));
+		return -1.0;
+	}
+	cudaEventDestroy(e0);
+	cudaEventDestroy(e1);
+	if (clk_out)
+		*clk_out = clk;
+	return tcups;
 }
 
 // Scheduler probe: ILP independent GA-shaped cells per thread (3 DPX + IMAD [+ LDS]), no strip
@@ -292,6 +303,60 @@ template <int MODE, int ILP> static void run_mix(const char *name, uint32_t *out
 	printf("%-44s warps/SMSP %d  %.2f clk/cell/SMSP\n", name, occ, best * 1e-3 * mhz * 1e6 / cells_per_smsp);
 }
 
+// Library entry (bench.py): TCUPS ceiling of the bare register block for `method` (0 NW, 1 GA,
+// 2 SW) and strip width (narrow = 16 columns / 5 blocks per SM, else 32 / 4) on `device`.
+static void make_letters(std::vector<uint32_t> &h)
+{
+	uint32_t s = 12345;
+	for (auto &w : h) {
+		uint32_t v = 0;
+		for (int b = 0; b < 4; b++) {
+			s = s * 1664525u + 1013904223u;
+			v |= (((s >> 16) % 20) * 4) << (8 * b);
+		}
+		w = v;
+	}
+}
+
+extern "C" int sab_cell_peak(int method, int narrow, int device, double *tcups, double *clk_per_cell_pair)
+{
+	if (method < 0 || method > 2 || !tcups)
+		return -1;
+	if (cudaSetDevice(device) != cudaSuccess)
+		return -2;
+	cudaDeviceProp prop;
+	if (cudaGetDeviceProperties(&prop, device) != cudaSuccess)
+		return -2;
+	int khz = 0;
+	cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device);
+	const double mhz = khz / 1e3;
+	uint32_t *out = nullptr, *letters = nullptr;
+	std::vector<uint32_t> h(64 * 32);
+	make_letters(h);
+	if (cudaMalloc(&out, sizeof(uint32_t) * prop.multiProcessorCount * 16 * 128) != cudaSuccess ||
+	    cudaMalloc(&letters, h.size() * 4) != cudaSuccess)
+		return -3;
+	cudaMemcpy(letters, h.data(), h.size() * 4, cudaMemcpyHostToDevice);
+	const int sms = prop.multiProcessorCount;
+	double v = -1.0;
+	const int key = method * 2 + (narrow ? 1 : 0);
+	switch (key) {
+	case 0: v = run<M_NW, 32, 4, true, true>(nullptr, out, letters, sms, mhz, 4, clk_per_cell_pair); break;
+	case 1: v = run<M_NW, 16, 5, true, true>(nullptr, out, letters, sms, mhz, 5, clk_per_cell_pair); break;
+	case 2: v = run<M_GA, 32, 4, true, true>(nullptr, out, letters, sms, mhz, 4, clk_per_cell_pair); break;
+	case 3: v = run<M_GA, 16, 5, true, true>(nullptr, out, letters, sms, mhz, 5, clk_per_cell_pair); break;
+	case 4: v = run<M_SW, 32, 4, true, true>(nullptr, out, letters, sms, mhz, 4, clk_per_cell_pair); break;
+	default: v = run<M_SW, 16, 5, true, true>(nullptr, out, letters, sms, mhz, 5, clk_per_cell_pair); break;
+	}
+	cudaFree(out);
+	cudaFree(letters);
+	if (v < 0)
+		return -4;
+	*tcups = v;
+	return 0;
+}
+
+#ifndef CELL_PEAK_LIB
 int main()
 {
 	cudaDeviceProp prop;
@@ -302,15 +367,7 @@ int main()
 	uint32_t *out, *letters;
 	cudaMalloc(&out, sizeof(uint32_t) * prop.multiProcessorCount * 16 * 128);
 	std::vector<uint32_t> h(64 * 32);
-	uint32_t s = 12345;
-	for (auto &w : h) {
-		uint32_t v = 0;
-		for (int b = 0; b < 4; b++) {
-			s = s * 1664525u + 1013904223u;
-			v |= (((s >> 16) % 20) * 4) << (8 * b);
-		}
-		w = v;
-	}
+	make_letters(h);
 	cudaMalloc(&letters, h.size() * 4);
 	cudaMemcpy(letters, h.data(), h.size() * 4, cudaMemcpyHostToDevice);
 	const int sms = prop.multiProcessorCount;
@@ -334,3 +391,4 @@ int main()
 	RUN(M_NW, 16, 8, true, false, 8, 0);
 	return 0;
 }
+#endif // CELL_PEAK_LIB
