@@ -414,7 +414,10 @@ def run_ours(args):
                 "note": "non-binding"},
     }
 
-    ceiling = measure_cell_ceiling(local_rank, method, float(store.lengths.mean()) < 160.0)
+    # same rule as plan_strips (sab_capi.cu): narrow strips only where they save enough padding
+    ln = store.lengths.astype(np.int64)
+    narrow = float(((ln + 15) // 16 * 16).sum()) * 1.055 < float(((ln + 31) // 32 * 32).sum())
+    ceiling = measure_cell_ceiling(local_rank, method, narrow)
     if ceiling:
         ceiling["kernel_frac_of_ceiling"] = cells_per_s_gpu / 1e9 / ceiling["gcups"]
     roofline["code_shape_ceiling"] = ceiling

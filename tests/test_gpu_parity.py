@@ -67,6 +67,22 @@ def test_vs_oracle_mixed_lengths(oracle_mod, method, kw, flags):
     assert bad.size == 0, (bad[:10], got[bad[:10]], want[bad[:10]])
 
 
+@pytest.mark.parametrize("method,kw", METHODS)
+@pytest.mark.parametrize("flags", [0, capi.SAB_FLAG_STRIP32, capi.SAB_FLAG_FORCE_INT32])
+def test_vs_oracle_short_sequences_large_work_items(oracle_mod, method, kw, flags):
+    """lengths 1..40: one or two strips per subject pair, so a work item takes 64..128 subjects
+    (adaptive chunk, sab_capi.cu) and many pairs share the SW running-maximum slots"""
+    rng = np.random.default_rng(11)
+    lens = rng.integers(1, 41, size=1500)
+    store = SeqStore.from_codes(rng.integers(0, 20, size=int(lens.sum())), lens, synth.PROTEIN20)
+    cfg = AlignConfig(method, "blosum62", **kw)
+    want, _ = oracle_mod.align_all(cfg.resolve(), store, triangular=True)
+    got, st = gpu_scores(cfg, store, triangular=True, panel=512, flags=flags)
+    assert st["pairs"] == store.pairs() and st["cells"] == store.cells()
+    bad = np.flatnonzero(got != want)
+    assert bad.size == 0, (bad[:10], got[bad[:10]], want[bad[:10]])
+
+
 @pytest.mark.parametrize("config", ["c1", "c2", "c3", "c4"])
 def test_vs_oracle_baseline_configs_scaled(oracle_mod, config):
     """BASELINE.json configs at a size the oracle finishes in seconds"""
