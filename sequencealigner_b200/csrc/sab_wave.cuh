@@ -25,15 +25,15 @@
 //     NW  V = H - g(r+c)      V = max3(Vdiag + (S - 2g), Vleft, Vup)               1 alu 1 fma
 //     GA  V = M - e(r+c)      X = max(Vleft + (o-e), Xleft)   Y = max(Vup + (o-e), Yup)
 //         (X, Y skewed too)   V = max3(Vdiag + (S - 2e), X, Y)                      3 alu 1 fma
-//     SW  V = M + o           Y = max3(Yup + e, Vup, 0)       X = max(Xleft + e, Vleft)
-//         (Y floored at 0)    M = max3(Vdiag + (S - o), X, Y)   V = M + o           3.5 alu 3 fma
+//     SW  V = M + o           D = max(Vdiag + (S - o), 0)  Y = max(Yup + e, Vup)  X = max(Xleft + e, Vleft)
+//         (floor on D only)   M = max3(D, X, Y)   V = M + o   best = max3(best, M, M')   4.5 alu 1 fma
 //   NW/GA borders become constants (0 resp. o-e) and the score is V + g|e * (Lq + Ls).
 //   SW keeps the unskewed form because its zero floor would turn into a per-cell value.
 //   An 8-row group is issued in ANTI-DIAGONAL order (row k works on column t-k at time t):
 //   the 2-3 instruction dependency chain of a cell is interleaved with seven independent
 //   ones, which is what lets 4-5 resident warps per scheduler keep the alu pipe busy
-//   (profiles/r1_ncu_wave_v1.md shows the serial order stalling at 65 % alu, r1_ncu_wave_v4.md
-//   the current 78 %).
+//   (profiles/r1_ncu_wave_v1.md shows the serial order stalling at 65 % alu; now GA 78 %,
+//   SW 88 %: r1_ncu_wave_v5_*.md; what this code shape can reach: r1_cell_shape_ceiling.md).
 //
 // One __syncthreads per step (8 rows x K columns x 2 cells per thread).
 #pragma once
@@ -41,20 +41,6 @@
 #include "sab_kernels.cuh"
 
 #include <type_traits>
-
-#ifndef SAB_ORDER
-#define SAB_ORDER 0
-#endif
-#if SAB_ORDER == 0 // anti-diagonal
-#define SAB_TT_END (K + NR - 1)
-#define SAB_CELL_COL const int c = tt - k;
-#elif SAB_ORDER == 1 // skewed by 2
-#define SAB_TT_END (K + 2 * (NR - 1))
-#define SAB_CELL_COL const int c = tt - 2 * k;
-#elif SAB_ORDER == 2 // row-major
-#define SAB_TT_END (K * NR)
-#define SAB_CELL_COL const int c = (tt / K == k) ? tt % K : -1;
-#endif
 
 namespace sab {
 
@@ -355,10 +341,10 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 						}
 						diag = b[NR - 1].x;
 #pragma unroll
-						for (int tt = 0; tt < SAB_TT_END; tt++) {
+						for (int tt = 0; tt < K + NR - 1; tt++) {
 #pragma unroll
 							for (int k = 0; k < NR; k++) {
-								SAB_CELL_COL
+								const int c = tt - k;
 								if (c < 0 || c >= K)
 									continue;
 								const uint32_t m = cell<METHOD, PACKED>(
