@@ -344,12 +344,18 @@ def run_ours(args):
     barrier()
     e2e_t0 = time.perf_counter()
     h2d = d2h = 0
+    e2e_steps = []  # per step: wall ms of the two calls and the library's own device span
     for _ in range(args.steps):
+        t_a = time.perf_counter()
         al.upload(store)
+        t_b = time.perf_counter()
         al.align(out=host_matrix, shard=rank, nshards=world)
+        t_c = time.perf_counter()
         st = al.stats()
         h2d, d2h = st["h2d_bytes"], st["d2h_bytes"]
         launches += st["launches"]
+        e2e_steps.append({"upload_ms": round((t_b - t_a) * 1e3, 2), "align_ms": round((t_c - t_b) * 1e3, 2),
+                          "device_ms": round(st["device_ms"], 2)})
     barrier()
     e2e_ms = (time.perf_counter() - e2e_t0) * 1e3 / args.steps
     e2e_ms, _ = reduce_over_ranks(e2e_ms, 0)
@@ -442,7 +448,7 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": "GCUPS", "ms_per_step": e2e_ms,
                 "pairs_per_s": desc["pairs"] / (e2e_ms * 1e-3),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "checksum": checksum},
+                "checksum": checksum, "steps_rank0": e2e_steps},
         "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
         "cli_end_to_end": cli,
     }

@@ -83,6 +83,7 @@ struct sab_ctx {
 	int64_t *d_col_off = nullptr, *d_grp_off = nullptr;
 	uint8_t *d_col_bytes = nullptr;
 	uint32_t *d_rowpack = nullptr;
+	size_t cap_seqs[6]{}; // bytes allocated behind the six pointers above (reused across uploads)
 	// execution
 	StripBuf buf[2];
 	void *stage[2] = { nullptr, nullptr };
@@ -118,6 +119,22 @@ int fail(sab_ctx *c, int code, const char *fmt, ...)
 	} while (0)
 
 typedef void (*tile_kernel_t)(const TileParams);
+
+// grow-only device buffer
+int ensure(sab_ctx *ctx, void **p, size_t *cap, size_t need, size_t elem)
+{
+	if (need <= *cap)
+		return SAB_OK;
+	cudaFree(*p);
+	*p = nullptr;
+	*cap = 0;
+	cudaError_t e = cudaMalloc(p, need * elem);
+	if (e != cudaSuccess)
+		return fail(ctx, SAB_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", need * elem,
+			    cudaGetErrorString(e));
+	*cap = need;
+	return SAB_OK;
+}
 
 // Kernel variants: [narrow] strip width 32 (4 resident blocks/SM) or 16 (5 blocks/SM).
 constexpr int kStripWide = 32, kStripNarrow = 16;
@@ -164,6 +181,8 @@ void free_seqs(sab_ctx *c)
 	c->d_col_off = c->d_grp_off = nullptr;
 	c->d_col_bytes = nullptr;
 	c->d_rowpack = nullptr;
+	for (size_t &cap : c->cap_seqs)
+		cap = 0;
 	c->uploaded = false;
 }
 
@@ -503,7 +522,7 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 		return fail(ctx, SAB_ERR_ARG, "need at least 2 sequences (SEQ_N_MIN, align.h:21)");
 	const double t0 = now_ms();
 	CU(cudaSetDevice(ctx->cfg.device));
-	free_seqs(ctx);
+	ctx->uploaded = false; // device buffers are kept and reused when large enough
 
 	int32_t real_max = 0;
 	int64_t letters = 0;
@@ -590,12 +609,19 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 		}
 	}
 
-	CU(cudaMalloc(&ctx->d_slot_len, sizeof(int32_t) * num));
-	CU(cudaMalloc(&ctx->d_slot_orig, sizeof(int32_t) * num));
-	CU(cudaMalloc(&ctx->d_col_off, sizeof(int64_t) * num));
-	CU(cudaMalloc(&ctx->d_grp_off, sizeof(int64_t) * ngroups));
-	CU(cudaMalloc(&ctx->d_col_bytes, col_bytes.size()));
-	CU(cudaMalloc(&ctx->d_rowpack, rowpack.size() * sizeof(uint32_t)));
+	// cudaFree / cudaMalloc per upload cost 0.1-0.25 s every few calls (measured): grow-only reuse
+	{
+		void **ptr[6] = { (void **)&ctx->d_slot_len, (void **)&ctx->d_slot_orig, (void **)&ctx->d_col_off,
+				  (void **)&ctx->d_grp_off, (void **)&ctx->d_col_bytes, (void **)&ctx->d_rowpack };
+		const size_t need[6] = { sizeof(int32_t) * num, sizeof(int32_t) * num, sizeof(int64_t) * num,
+					 sizeof(int64_t) * ngroups, col_bytes.size(),
+					 rowpack.size() * sizeof(uint32_t) };
+		for (int i = 0; i < 6; i++) {
+			const int rc = ensure(ctx, ptr[i], &ctx->cap_seqs[i], need[i], 1);
+			if (rc)
+				return rc;
+		}
+	}
 	CU(cudaMemcpy(ctx->d_slot_len, slot_len.data(), sizeof(int32_t) * num, cudaMemcpyHostToDevice));
 	CU(cudaMemcpy(ctx->d_slot_orig, slot_orig.data(), sizeof(int32_t) * num,
 		      cudaMemcpyHostToDevice));
@@ -636,20 +662,6 @@ struct Strip {
 	double mean_ls; // mean subject length (strip width and chunk size heuristics)
 };
 
-int ensure(sab_ctx *ctx, void **p, size_t *cap, size_t need, size_t elem)
-{
-	if (need <= *cap)
-		return SAB_OK;
-	cudaFree(*p);
-	*p = nullptr;
-	*cap = 0;
-	cudaError_t e = cudaMalloc(p, need * elem);
-	if (e != cudaSuccess)
-		return fail(ctx, SAB_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", need * elem,
-			    cudaGetErrorString(e));
-	*cap = need;
-	return SAB_OK;
-}
 
 // Row strips (one per panel), their cost, and the longest-processing-time assignment
 // of strips to shards (deterministic: every rank computes the same plan).
