@@ -52,7 +52,11 @@ constexpr int kWaveThreads = kWaveWarps * 32;
 constexpr int kGroup = SAB_KGROUP; // rows per step (multiple of 4: rowpack holds 4 letters per word)
 constexpr int kGroupWords = kGroup / 4;
 constexpr int kBestSlots = 16; // subject pairs whose SW maxima can be in flight
-constexpr int kMinSteps = 6; // steps per round (>= 4 for the double-buffered staging)
+// Steps per round: round r+1 is staged at step 3 of round r, the earliest step at which warp 3 has
+// left round r-1 (whose profile buffer it overwrites), and must be done before warp 0 enters round
+// r+1 at step G; the wrap-around boundary written by warp 3 at step g+3 is read by warp 0 G-3 steps
+// later.  Both need G >= 4.
+constexpr int kMinSteps = 4;
 
 template <int K> struct WaveSmem {
 	uint32_t prof[2][kWaveWarps][K][kProfStride]; // strip profiles, parity = round & 1
