@@ -121,6 +121,24 @@ def test_no_write_mode_and_stats():
     assert st["d2h_bytes"] == 0 and st["kernel_ms"] > 0 and st["launches"] >= 1
 
 
+@pytest.mark.parametrize("method,kw", METHODS)
+def test_reupload_on_one_context_grow_and_shrink(oracle_mod, method, kw):
+    """sab_upload keeps its device buffers and re-uses them when they are large enough: results
+    of small -> large -> small uploads on ONE context must equal fresh-context results"""
+    small, _ = synth.make("c4", n=300)
+    large, _ = synth.make("c2", n=260)
+    cfg = AlignConfig(method, "blosum62", **kw)
+    want_small, _ = oracle_mod.align_all(cfg.resolve(), small, triangular=True)
+    want_large, _ = oracle_mod.align_all(cfg.resolve(), large, triangular=True)
+    with Aligner(cfg) as al:
+        for store, want in ((small, want_small), (large, want_large), (small, want_small),
+                            (large, want_large)):
+            al.upload(store)
+            got = al.align(triangular=True)
+            assert np.array_equal(got, want)
+            assert al.stats()["pairs"] == store.pairs()
+
+
 def test_sw_int16_overflow_rerun(oracle_mod):
     """C5-ovf: poly-W under pam500 exceeds int16 -> a-posteriori int32 re-run list"""
     store, c = synth.make_overflow(n=300, planted=6)
