@@ -131,7 +131,9 @@ const char *sab_last_error(const sab_ctx *ctx);
  * `max` is the longest length (== struct input, src/io/input.h:6-11).  The
  * letters are mapped through seq_lut, length-binned (stable sort inside each
  * panel) and packed into the two device layouts of DESIGN.md section 3.  The
- * host buffers are not referenced after return.
+ * host buffers are not referenced after return.  May be called again on the
+ * same context (a new set replaces the old one; device buffers are re-used
+ * when large enough and released by sab_destroy).
  */
 int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t num,
 	       int32_t max);
