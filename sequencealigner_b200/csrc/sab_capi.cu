@@ -208,6 +208,23 @@ struct Seg {
 	size_t n;
 };
 
+// Runs fn(first, last) over [0, n) split into contiguous ranges on up to 8 host threads
+// (`work` = total units, to stay single-threaded for small inputs).
+template <typename F> void parallel_ranges(int32_t n, int64_t work, F fn)
+{
+	const unsigned hw = std::thread::hardware_concurrency();
+	const int nthreads = (int)std::min<int64_t>(std::max(1u, std::min(hw, 8u)), work / (1 << 19) + 1);
+	if (nthreads <= 1 || n < nthreads) {
+		fn(0, n);
+		return;
+	}
+	std::vector<std::thread> th;
+	for (int t = 0; t < nthreads; t++)
+		th.emplace_back([=]() { fn((int32_t)((int64_t)n * t / nthreads), (int32_t)((int64_t)n * (t + 1) / nthreads)); });
+	for (auto &x : th)
+		x.join();
+}
+
 void copy_segments(const std::vector<Seg> &segs)
 {
 	size_t total = 0;
@@ -571,19 +588,25 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 
 	// Subject layout: one byte per residue, index 0..23.
 	std::vector<uint8_t> col_bytes((size_t)letters + 16, 24);
-	for (int32_t s = 0; s < num; s++) {
-		const uint8_t *src = seqs + meta[slot_orig[s]].off;
-		uint8_t *dst = col_bytes.data() + col_off[s];
-		for (int32_t k = 0; k < slot_len[s]; k++) {
-			const uint8_t ch = src[k];
-			const int32_t idx = ch < 128 ? ctx->cfg.seq_lut[ch] : -1;
-			if (idx < 0 || idx >= 24)
-				return fail(ctx, SAB_ERR_ARG,
-					    "sequence %d has a letter outside the matrix alphabet",
-					    slot_orig[s]);
-			dst[k] = (uint8_t)idx;
+	std::atomic<int32_t> bad_seq{ -1 };
+	parallel_ranges(num, letters, [&](int32_t s0, int32_t s1) {
+		for (int32_t s = s0; s < s1; s++) {
+			const uint8_t *src = seqs + meta[slot_orig[s]].off;
+			uint8_t *dst = col_bytes.data() + col_off[s];
+			for (int32_t k = 0; k < slot_len[s]; k++) {
+				const uint8_t ch = src[k];
+				const int32_t idx = ch < 128 ? ctx->cfg.seq_lut[ch] : -1;
+				if (idx < 0 || idx >= 24) {
+					bad_seq.store(slot_orig[s]);
+					return;
+				}
+				dst[k] = (uint8_t)idx;
+			}
 		}
-	}
+	});
+	if (bad_seq.load() >= 0)
+		return fail(ctx, SAB_ERR_ARG, "sequence %d has a letter outside the matrix alphabet",
+			    bad_seq.load());
 	// Query layout: 32-slot groups, 4 residues per word (stored as byte offsets
 	// letter*4 into a profile column), lane-interleaved for coalesced loads.
 	const int ngroups = (num + 31) / 32;
@@ -599,15 +622,17 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 	}
 	// rows past a sequence's end hold the pad letter (24): SW sweeps them (sab_wave.cuh)
 	std::vector<uint32_t> rowpack((size_t)rows4 * 32, 0x60606060u);
-	for (int32_t s = 0; s < num; s++) {
-		const uint8_t *src = col_bytes.data() + col_off[s];
-		uint32_t *dst = rowpack.data() + grp_off[s >> 5] * 32 + (s & 31);
-		for (int32_t r = 0; r < slot_len[s]; r++) {
-			uint32_t &wd = dst[(size_t)(r >> 2) * 32];
-			const int sh = 8 * (r & 3);
-			wd = (wd & ~(0xffu << sh)) | ((uint32_t)(src[r] * 4) << sh);
+	parallel_ranges(num, letters, [&](int32_t s0, int32_t s1) { // every slot owns its own words
+		for (int32_t s = s0; s < s1; s++) {
+			const uint8_t *src = col_bytes.data() + col_off[s];
+			uint32_t *dst = rowpack.data() + grp_off[s >> 5] * 32 + (s & 31);
+			for (int32_t r = 0; r < slot_len[s]; r++) {
+				uint32_t &wd = dst[(size_t)(r >> 2) * 32];
+				const int sh = 8 * (r & 3);
+				wd = (wd & ~(0xffu << sh)) | ((uint32_t)(src[r] * 4) << sh);
+			}
 		}
-	}
+	});
 
 	// cudaFree / cudaMalloc per upload cost 0.1-0.25 s every few calls (measured): grow-only reuse
 	{
