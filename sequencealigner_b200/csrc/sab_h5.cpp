@@ -419,70 +419,108 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 		std::vector<ChunkRec> recs;
 		recs.reserve(nc * nc);
 		unsigned hw = std::thread::hardware_concurrency();
-		const size_t nthreads = std::max<size_t>(1, std::min<size_t>({ (size_t)(hw ? hw : 4), 32, nc }));
-		// one chunk row at a time: gather + deflate in parallel, write in order
+		const size_t total = nc * nc; // chunks in row-major order (the order they are written in)
+		const size_t nthreads = std::max<size_t>(1, std::min<size_t>({ (size_t)(hw ? hw : 4), 16, total }));
+		// Batches of `nthreads` chunks across chunk-row boundaries, two slot sets: batch b+1 is
+		// gathered + deflated while the calling thread appends batch b to the file, in order.
 		struct Slot {
 			std::vector<int32_t> raw;
 			std::vector<uint8_t> z;
 			size_t zlen = 0;
 			bool err = false;
 		};
-		std::vector<Slot> slots(nthreads);
+		std::vector<Slot> slots(std::min(total, 2 * nthreads));
 		for (auto &s : slots) {
 			s.raw.resize(cdim * cdim);
 			if (deflate)
 				s.z.resize(compressBound(raw_bytes));
 		}
-		for (size_t cr = 0; cr < nc && F.ok; cr++) {
-			for (size_t c0 = 0; c0 < nc && F.ok; c0 += nthreads) {
-				const size_t nb = std::min(nthreads, nc - c0);
-				std::vector<std::thread> th;
-				for (size_t t = 0; t < nb; t++) {
-					th.emplace_back([&, t]() {
-						Slot &s = slots[t];
-						const uint64_t R0 = cr * cdim, C0 = (c0 + t) * cdim;
-						for (size_t r = 0; r < cdim; r++) {
-							int32_t *dst = s.raw.data() + r * cdim;
-							const uint64_t R = R0 + r;
-							if (R >= dim) { // edge chunks are stored whole, padded with 0
-								memset(dst, 0, cdim * 4);
-								continue;
-							}
-							const size_t w = (size_t)std::min<uint64_t>(cdim, dim - C0);
-							if (!tri) {
-								memcpy(dst, matrix + R * dim + C0, w * 4);
-							} else {
-								for (size_t c = 0; c < w; c++)
-									dst[c] = cell_at(matrix, true, dim, R, C0 + c);
-							}
-							if (w < cdim)
-								memset(dst + w, 0, (cdim - w) * 4);
+		auto work = [&](const size_t idx, Slot &s) {
+			const size_t cr = idx / nc, cc = idx % nc;
+			const uint64_t R0 = cr * cdim, C0 = cc * cdim;
+			if (tri && cc > cr) {
+				// block strictly above the diagonal: element (R, C) is packed-row C, column R
+				// (src/io/output.c:83), i.e. the transpose of contiguous runs -> 32 x 32 tiles
+				const size_t h = (size_t)std::min<uint64_t>(cdim, dim - R0);
+				const size_t w = (size_t)std::min<uint64_t>(cdim, dim - C0);
+				if (h < cdim || w < cdim)
+					memset(s.raw.data(), 0, raw_bytes);
+				for (size_t c0 = 0; c0 < w; c0 += 32)
+					for (size_t r0 = 0; r0 < h; r0 += 32) {
+						const size_t ce = std::min(w, c0 + 32), re = std::min(h, r0 + 32);
+						for (size_t c = c0; c < ce; c++) {
+							const uint64_t C = C0 + c;
+							const int32_t *src = matrix + C * (C - 1) / 2 + R0;
+							for (size_t r = r0; r < re; r++)
+								s.raw[r * cdim + c] = src[r];
 						}
-						if (deflate) {
-							uLongf zl = (uLongf)s.z.size();
-							s.err = compress2(s.z.data(), &zl, (const Bytef *)s.raw.data(),
-									  (uLong)raw_bytes, (int)compression) != Z_OK;
-							s.zlen = zl;
-						}
-					});
-				}
-				for (auto &t : th)
-					t.join();
-				for (size_t t = 0; t < nb; t++) {
-					Slot &s = slots[t];
-					if (s.err) {
-						fclose(F.f);
-						return SAB_ERR_NOMEM;
 					}
-					const void *p = deflate ? (const void *)s.z.data() : (const void *)s.raw.data();
-					const size_t n = deflate ? s.zlen : raw_bytes;
-					const uint64_t a = F.append(p, n);
-					recs.push_back({ a, (uint32_t)n, cr * cdim, (c0 + t) * cdim });
+			} else
+			for (size_t r = 0; r < cdim; r++) {
+				int32_t *dst = s.raw.data() + r * cdim;
+				const uint64_t R = R0 + r;
+				if (R >= dim) { // edge chunks are stored whole, padded with 0
+					memset(dst, 0, cdim * 4);
+					continue;
 				}
+				const size_t w = (size_t)std::min<uint64_t>(cdim, dim - C0);
+				if (!tri) {
+					memcpy(dst, matrix + R * dim + C0, w * 4);
+				} else if (cc < cr) { // strictly below the diagonal: a run of packed row R
+					memcpy(dst, matrix + R * (R - 1) / 2 + C0, w * 4);
+				} else {
+					for (size_t c = 0; c < w; c++)
+						dst[c] = cell_at(matrix, true, dim, R, C0 + c);
+				}
+				if (w < cdim)
+					memset(dst + w, 0, (cdim - w) * 4);
 			}
-			if (progress)
-				progress((int64_t)(cr + 1), (int64_t)nc, user);
+			if (deflate) {
+				uLongf zl = (uLongf)s.z.size();
+				s.err = compress2(s.z.data(), &zl, (const Bytef *)s.raw.data(), (uLong)raw_bytes,
+						  (int)compression) != Z_OK;
+				s.zlen = zl;
+			}
+		};
+		auto launch = [&](const size_t base, const size_t set, std::vector<std::thread> &th) {
+			const size_t nb = std::min(nthreads, total - base);
+			for (size_t t = 0; t < nb; t++)
+				th.emplace_back([&work, &slots, base, set, t, nthreads]() {
+					work(base + t, slots[(set * nthreads + t) % slots.size()]);
+				});
+		};
+		std::vector<std::thread> cur, nxt;
+		size_t set = 0;
+		launch(0, set, cur);
+		for (size_t base = 0; base < total;) {
+			const size_t nb = std::min(nthreads, total - base);
+			if (base + nb < total && F.ok)
+				launch(base + nb, set ^ 1, nxt);
+			for (auto &t : cur)
+				t.join();
+			cur.clear();
+			for (size_t t = 0; t < nb && F.ok; t++) {
+				Slot &s = slots[(set * nthreads + t) % slots.size()];
+				if (s.err) {
+					for (auto &x : nxt)
+						x.join();
+					fclose(F.f);
+					return SAB_ERR_NOMEM;
+				}
+				const size_t idx = base + t;
+				const void *p = deflate ? (const void *)s.z.data() : (const void *)s.raw.data();
+				const size_t n = deflate ? s.zlen : raw_bytes;
+				const uint64_t a = F.append(p, n);
+				recs.push_back({ a, (uint32_t)n, (idx / nc) * cdim, (idx % nc) * cdim });
+				if (progress && (idx + 1) % nc == 0)
+					progress((int64_t)((idx + 1) / nc), (int64_t)nc, user);
+			}
+			cur.swap(nxt);
+			base += nb;
+			set ^= 1;
 		}
+		for (auto &t : cur) // only reached with threads left after a write error
+			t.join();
 		a_mat = write_chunk_tree(F, recs, cdim);
 	}
 
