@@ -114,10 +114,13 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
-def workload(config: str, n_gpus: int, n_override: int | None, method: str | None = None):
+def workload(config: str, n_gpus: int, n_override: int | None, method: str | None = None,
+             scaling: str = "weak"):
+    """The synthetic set + CLI-level configuration.  weak: the sequence count grows with sqrt(N)
+    so the pairs per GPU stay fixed; strong: BASELINE.json's size at every N."""
     from sequencealigner_b200 import AlignConfig, synth
     base = synth.CONFIGS[config]
-    n = n_override or int(round(base["n"] * np.sqrt(n_gpus)))
+    n = n_override or (base["n"] if scaling == "strong" else int(round(base["n"] * np.sqrt(n_gpus))))
     store, c = synth.make(config, n=n)
     if method and method != c["method"]:  # informational runs: same sequences, other recurrence
         c = {k: v for k, v in c.items() if k not in ("gap_pen", "gap_open", "gap_ext")}
@@ -128,7 +131,8 @@ def workload(config: str, n_gpus: int, n_override: int | None, method: str | Non
     desc = {"workload": f"{config}: synthetic {'DNA' if c['alphabet'] == 'ACGT' else 'protein'} "
                         f"{n} seqs len {c['lo']}..{c['hi']}, -a {c['method']} -m {c['matrix']} "
                         + (f"-p {c['gap_pen']}" if "gap_pen" in c else
-                           f"-s {c['gap_open']} -e {c['gap_ext']}"),
+                           f"-s {c['gap_open']} -e {c['gap_ext']}")
+                        + (f" -f {c['filter']}" if c.get("filter") else ""),
             "sequences": n, "pairs": store.pairs(), "cells": store.cells(),
             "seed": c["seed"], "layout": "packed-triangular int32"}
     return store, cfg, c, desc
@@ -143,9 +147,11 @@ def cpu_reference_sample(store, c, target_s: float = 15.0):
     the first M sequences of the workload, M sized for ~target_s of CPU work.  Falls back
     to the oracle port (liboracle.so, OpenMP) when the reference binary is not there."""
     from oracle import oracle
-    cores = os.cpu_count() or 1
-    cli = oracle.ref_args(c["method"], c["matrix"], gap_pen=c.get("gap_pen"),
-                          gap_open=c.get("gap_open"), gap_ext=c.get("gap_ext"))
+    from sequencealigner_b200 import synth
+    cores = len(os.sched_getaffinity(0)) or os.cpu_count() or 1
+    cli = synth.cli_args(c["method"], c["matrix"], gap_pen=c.get("gap_pen"),
+                         gap_open=c.get("gap_open"), gap_ext=c.get("gap_ext"))
+    seen = {"threads": None, "binary": None}
 
     def run(m):
         sub = store.head(m)
@@ -153,10 +159,12 @@ def cpu_reference_sample(store, c, target_s: float = 15.0):
             with tempfile.TemporaryDirectory() as td:
                 fa = Path(td) / "sample.fasta"
                 sub.to_fasta(fa)
+                # threads=0 -> "-T <host cores>", OMP_* scrubbed from the child's environment
                 r = oracle.run_reference(fa, cli, threads=0, write=False, bench=True)
             secs = r["align_seconds"]
             if not secs or secs <= 0:
                 raise RuntimeError("could not read 'Alignment: X sec' from the reference")
+            seen["threads"], seen["binary"] = r["threads"], r["binary"]
             return sub.cells(), secs, "reference"
         from sequencealigner_b200 import AlignConfig
         r = AlignConfig(c["method"], c["matrix"], gap_pen=c.get("gap_pen"),
@@ -174,9 +182,12 @@ def cpu_reference_sample(store, c, target_s: float = 15.0):
         cells, secs, kind = run(m)
     else:
         m = m0
-    return {"value": cells / secs / 1e9, "unit": "GCUPS", "cores": cores, "kind": kind,
+    threads = seen["threads"] or cores
+    return {"value": cells / secs / 1e9, "unit": "GCUPS", "cores": threads, "kind": kind,
             "sample": f"first {m} of {store.num} sequences ({cells:.3e} cells, {secs:.2f} s "
-                      f"alignment time, threads=all)", "_cells": cells, "_secs": secs, "_m": m}
+                      f"alignment time; the reference reports 'CPU Threads: {seen['threads']}' on "
+                      f"{cores} host cores; binary oracle/_ref/{seen['binary']})",
+            "_cells": cells, "_secs": secs, "_m": m}
 
 
 def cli_end_to_end(store, c, binary, threads=0, extra=()):
@@ -188,23 +199,36 @@ def cli_end_to_end(store, c, binary, threads=0, extra=()):
     try:
         fa = Path(td) / "in.fasta"
         store.to_fasta(fa)
-        from oracle import oracle  # only for the flag spelling (ref_args); nothing is computed there
+        from sequencealigner_b200 import synth
         out = Path(td) / "out.h5"
-        cmd = [str(binary), "-i", str(fa), "-o", str(out), *oracle.ref_args(**c), "-F", "-P", "-B",
-               "-T", str(threads), *extra]
+        nthreads = threads or len(os.sched_getaffinity(0)) or 1
+        cmd = [str(binary), "-i", str(fa), "-o", str(out), *synth.cli_args(**c), "-F", "-P", "-B",
+               "-T", str(nthreads), *extra]
+        env = {k: v for k, v in os.environ.items() if not k.startswith(("OMP_", "GOMP_", "KMP_"))}
         t0 = time.perf_counter()
-        p = subprocess.run(cmd, capture_output=True, text=True)
+        p = subprocess.run(cmd, capture_output=True, text=True, env=env)
         wall = time.perf_counter() - t0
         if p.returncode != 0:
             return {"error": (p.stdout + p.stderr)[-300:]}
-        m = re.search(r"Alignment:\s*([0-9.]+)\s*sec", p.stdout)
+
+        def sec(name):
+            m = re.search(name + r":\s*([0-9.]+)\s*sec", p.stdout)
+            return float(m.group(1)) if m else None
         dev = re.search(r"Using (\d+) B200", p.stdout)
-        return {"pairs_per_s": store.pairs() / wall, "wall_s": wall,
-                "align_s": float(m.group(1)) if m else None,
+        lost = re.search(r"Filtered out (\d+) sequences", p.stdout)  # filter.c:81
+        n_after = store.num - (int(lost.group(1)) if lost else 0)
+        pairs = n_after * (n_after - 1) // 2  # the pairs the run actually scored and wrote
+        return {"pairs_per_s": pairs / wall, "wall_s": wall, "pairs": pairs,
+                "sequences_in": store.num, "sequences_after_filter": n_after,
+                "split_s": {"input": sec("Input"), "filter": sec("Filtering"),
+                            "align": sec("Alignment"), "output": sec("Output")},
+                "align_s": sec("Alignment"),
                 "output_bytes": out.stat().st_size if out.exists() else 0,
-                "devices": int(dev.group(1)) if dev else 0,
+                "devices": int(dev.group(1)) if dev else 0, "host_threads": nthreads,
+                "args": " ".join(cmd[5:]),
                 "what": "integration/_build/seqalign_b200 (unmodified reference host + this "
-                        "library): FASTA parse + alignment + HDF5 write, wall clock"}
+                        "library): FASTA parse + filter + alignment + HDF5 write, wall clock; "
+                        "split_s = the reference's own -B timers"}
     finally:
         shutil.rmtree(td, ignore_errors=True)
 
@@ -213,7 +237,7 @@ def run_reference_arm(args):
     rank, _, world = dist_env()
     if rank != 0:
         return 0
-    store, cfg, c, desc = workload(args.config, args.gpus, args.n, args.method)
+    store, cfg, c, desc = workload(args.config, args.gpus, args.n, args.method, args.scaling)
     per_step = max(4.0, min(20.0, 150.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
         cpu_reference_sample(store, c, target_s=per_step)
@@ -228,7 +252,8 @@ def run_reference_arm(args):
     base["value"] = value
     out = {"impl": "reference", "metric": "all-vs-all GCUPS", "value": value, "unit": "GCUPS",
            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-           "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+           "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True,
+           "scaling": args.scaling,
            "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": desc,
            "cpu_baseline": base,
            "e2e": {"value": value, "unit": "GCUPS", "h2d_bytes_per_step": 0,
@@ -296,9 +321,10 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_gpus = world
 
-    store, cfg, c, desc = workload(args.config, n_gpus, args.n, args.method)
-    desc["parallelism"] = f"row-strip shards x{n_gpus}, no collective"
-    desc["l2_flush"] = "512 MiB device memset between timed steps"
+    store, cfg, c, desc = workload(args.config, n_gpus, args.n, args.method, args.scaling)
+    # `config` is kept identical to the reference arm's; what is specific to this arm goes beside it
+    parallelism = f"row-strip shards x{n_gpus}, no collective"
+    l2_flush = "512 MiB device memset between timed steps"
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
 
     def barrier():
@@ -441,8 +467,8 @@ def run_ours(args):
     out = {
         "metric": "all-vs-all GCUPS", "value": value, "unit": "GCUPS", "n_gpus": n_gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16x2",
-        "data": "synthetic", "config": desc,
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int16x2",
+        "data": "synthetic", "config": desc, "parallelism": parallelism, "l2_flush": l2_flush,
         "pairs_per_s": desc["pairs"] / (step_ms * 1e-3),
         "wall_ms_per_step": wall_ms / args.steps,
         "e2e": {"value": e2e_value, "unit": "GCUPS", "ms_per_step": e2e_ms,
@@ -466,6 +492,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5"])
     ap.add_argument("--n", type=int, default=None, help="override the sequence count")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: sequences x sqrt(gpus) (default, the driver's SCALE run); strong: "
+                         "the config's own size at every N (BASELINE.json quotes C3 at 1/2/4/8)")
     ap.add_argument("--method", default=None, choices=["nw", "ga", "sw"],
                     help="override the config's alignment method (informational runs)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -22,7 +22,7 @@
  *        <- the batched launch + D2H loop    src/interface/seqalign_cuda.c:134-294
  *           and, semantically, align() + output_fill()
  *                                            src/bio/align.c:21-72, src/io/output.c:68-84
- *   sab_filter
+ *   sab_filter / sab_filter_matches + sab_filter_resolve / sab_multi_filter
  *        <- filter() decisions               src/bio/filter.c:14-62 (sequential -T 1 semantics)
  *   sab_matrix_lookup
  *        <- parse_matrix                     src/bio/matrices.c:44-57
@@ -56,7 +56,9 @@ enum sab_status {
 	SAB_ERR_CUDA = -3, /* CUDA runtime error, see sab_last_error */
 	SAB_ERR_NOMEM = -4, /* host or device allocation failed */
 	SAB_ERR_STATE = -5, /* call order violated (e.g. align before upload) */
-	SAB_ERR_OVERFLOW = -6, /* int16 re-run list overflowed (internal, retried) */
+	SAB_ERR_OVERFLOW = -6, /* sab_filter_matches only: more matching pairs than the caller's list holds
+				* (the alignment path never returns it: an SW strip whose int16 re-run
+				* list runs full is swept again in int32) */
 };
 
 /* src/bio/method/{nw,ga,sw}.c */
@@ -73,6 +75,12 @@ enum sab_flags {
 	SAB_FLAG_FORCE_INT16 = 2, /* testing: skip the a-priori range test (SW still re-runs) */
 	SAB_FLAG_STRIP32 = 8, /* testing/tuning: always use the 32-column register-strip kernel */
 	SAB_FLAG_STRIP16 = 16, /* testing/tuning: always use the 16-column register-strip kernel */
+	SAB_FLAG_ORDERED = 32, /* issue row strips in ascending row order instead of costliest first: the
+				* writes into `matrix` then advance through ascending offsets (a file-backed
+				* MAP_SHARED sink, src/io/output.c:35-55, gets sequential write-back) */
+	SAB_FLAG_TEST_RERUN_CAP = 64, /* testing: SW int16 re-run list of 4 entries (exercises the int32 re-sweep) */
+	SAB_FLAG_FILTER_SEQUENTIAL = 128, /* testing/tuning: sab_filter takes the panel-sequential path directly */
+	SAB_FLAG_TEST_FILTER_CAP = 256, /* testing: filter match list of 16 entries (exercises the fallback) */
 };
 
 typedef struct sab_config {
@@ -83,7 +91,7 @@ typedef struct sab_config {
 	int32_t seq_lut[128]; /* SEQ_LUT, ASCII -> index or -1 (src/bio/matrices.c:12) */
 	int32_t sub_mat[24 * 24]; /* SUB_MAT, must be symmetric (src/bio/matrices.c:13) */
 	int32_t device; /* CUDA device ordinal this context drives */
-	int32_t panel; /* sequences per panel, multiple of 32; 0 = auto */
+	int32_t panel; /* sequences per panel (= rows per row strip), multiple of 128; 0 = auto */
 	int32_t flags; /* enum sab_flags */
 	int32_t shards_hint; /* how many shards sab_align_shard will be called with (sizes the
 			      * auto panel so every shard gets several row strips); 0 = 1 */
@@ -106,7 +114,9 @@ typedef struct sab_stats {
 	int64_t tiles_int32; /* panel tiles routed wholesale to the int32 kernel */
 	int64_t h2d_bytes; /* bytes copied host->device by the last sab_upload */
 	int64_t d2h_bytes; /* bytes copied device->host by the last sab_align* */
-	int64_t reserved[3];
+	int64_t rerun_strips; /* SW strips swept again in int32 because their re-run list ran full */
+	int64_t filter_matches; /* pairs that passed the threshold in the last sab_filter* (-1: sequential path) */
+	double filter_ms; /* wall time of the last sab_filter* / sab_multi_filter */
 } sab_stats;
 
 typedef struct sab_ctx sab_ctx;
@@ -116,9 +126,11 @@ typedef void (*sab_progress_fn)(int64_t pairs_done, int64_t pairs_total, void *u
 
 int sab_abi_version(void);
 
-/* Number of usable CUDA devices (0 when none / driver missing). */
+/* Number of usable CUDA devices, i.e. of compute capability 10.x (0 when none / driver missing). */
 int sab_device_count(void);
-/* cudaMemGetInfo of `device`. */
+/* CUDA ordinal of the index-th usable device (what sab_config.device takes), or SAB_ERR_NODEVICE. */
+int sab_device_ordinal(int index);
+/* cudaMemGetInfo of CUDA ordinal `device`. */
 int sab_device_memory(int device, size_t *free_bytes, size_t *total_bytes);
 
 int sab_create(sab_ctx **ctx, const sab_config *cfg);
@@ -179,8 +191,11 @@ int sab_get_stats(const sab_ctx *ctx, sab_stats *out);
 /*
  * Every GPU of the box from one host process (what cuda_align needs: it is called once, on
  * the main thread, src/main.c:31): one context and one host thread per device, each device
- * holds a replica of the sequence set and fills its own shard of row strips of the caller's
- * matrix -- sab_align_shard(k, ndev) on device k.  No collective.  ndev <= 0 = all devices.
+ * holds a replica of the sequence set and pulls row strips (costliest first) from a cursor the
+ * devices share, writing them into the caller's matrix.  No collective.
+ * ndev > 0: exactly that many devices.  ndev <= 0: as many as the job can keep busy -- contexts
+ * are created lazily, in parallel, when sab_multi_upload / sab_multi_filter know the job's
+ * size (a context costs the host a few hundred ms; a small job is faster on one device).
  * Stats: counts are summed over the devices, times are the slowest device's.  The progress
  * callback is serialised and reports pairs over the whole job.
  */
@@ -193,6 +208,9 @@ int sab_multi_upload(sab_multi *m, const uint8_t *seqs, const sab_meta *meta, in
 		     int32_t max);
 int sab_multi_align(sab_multi *m, int32_t *matrix, int triangular, sab_progress_fn progress,
 		    void *user);
+/* sab_filter on the devices of `m`: phase A sharded over the devices, phase B on the host. */
+int sab_multi_filter(sab_multi *m, const uint8_t *seqs, const sab_meta *meta, int32_t num,
+		     float threshold, uint8_t *lost);
 int sab_multi_get_stats(const sab_multi *m, sab_stats *out);
 
 /*
@@ -204,6 +222,19 @@ int sab_multi_get_stats(const sab_multi *m, sab_stats *out);
  */
 int sab_filter(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t num,
 	       float threshold, uint8_t *lost);
+/*
+ * The two phases of sab_filter, for hosts that spread the filter over several devices or
+ * processes.  Phase A (device): every pair i<j of shard `shard` of `nshards` (tiles of 32 j's,
+ * dealt out so the shards' loads stay level) with (float)matches/(float)min(len) >= threshold,
+ * written as (j << 32 | i) in no particular order; *count receives how many.  More than `cap`
+ * -> SAB_ERR_OVERFLOW (use sab_filter, whose panel-sequential path handles any density).
+ * Phase B (host only): the order-dependent recurrence of filter.c:35-55 over the concatenated
+ * lists of all shards; returns the number of lost sequences.
+ */
+int sab_filter_matches(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t num,
+		       float threshold, int32_t shard, int32_t nshards, uint64_t *pairs, int64_t cap,
+		       int64_t *count);
+int sab_filter_resolve(int32_t num, const uint64_t *pairs, int64_t count, uint8_t *lost);
 
 /* Built-in substitution tables (host only, no device needed). */
 int sab_matrix_count(void);

@@ -54,6 +54,12 @@ void kernel_sw(s32 *, s64, s64)
 
 static bool no_cuda; /* -C: the user asked for the reference's CPU path */
 static int device_count = -1;
+static sab_multi *multi; /* one set of device contexts for the filter and the alignment */
+
+bool b200_cuda_disabled(void)
+{
+	return no_cuda;
+}
 
 static bool device_probe(void)
 {
@@ -83,7 +89,7 @@ bool cuda_memory(size_t bytes)
 	if (!device_probe())
 		exit(EXIT_FAILURE);
 	size_t free_b = 0, total_b = 0;
-	if (sab_device_memory(0, &free_b, &total_b) != SAB_OK) {
+	if (sab_device_memory(sab_device_ordinal(0), &free_b, &total_b) != SAB_OK) {
 		perr("Failed to query device memory");
 		exit(EXIT_FAILURE);
 	}
@@ -109,43 +115,63 @@ static void on_progress(int64_t done, int64_t total, void *)
 	pproportc(done / total, "Aligning sequences");
 }
 
-bool cuda_align(struct input in, struct output out)
+static void context_release(void)
 {
-	if (no_cuda)
-		return align(in, out);
-	if (!device_probe())
-		return false;
+	sab_multi_destroy(multi);
+	multi = nullptr;
+}
 
+/*
+ * The B200s of the box behind one handle: a context + host thread per device, created lazily
+ * by the library and only as many as the job can keep busy.  Shared by filter() (which runs
+ * first, inside input_load) and cuda_align().  All arguments are parsed by then, so ALIGN,
+ * SEQ_LUT, SUB_MAT and the gap values are final.
+ */
+sab_multi *b200_context(void)
+{
+	if (multi)
+		return multi;
+	if (!device_probe())
+		return nullptr;
 	sab_config cfg = {
 		.method = method_id(),
-		.gap_pen = GAP_PEN,
-		.gap_open = GAP_OPN,
-		.gap_ext = GAP_EXT,
-		.device = 0,
+		/* validate_ga parks the unused values at SCORE_MIN when it switches to NW (ga.c:83-84) */
+		.gap_pen = GAP_PEN == SCORE_MIN ? 0 : GAP_PEN,
+		.gap_open = GAP_OPN == SCORE_MIN ? 0 : GAP_OPN,
+		.gap_ext = GAP_EXT == SCORE_MIN ? 0 : GAP_EXT,
 	};
 	if (cfg.method < 0) {
 		perr("Alignment method has no B200 kernel");
-		return false;
+		return nullptr;
 	}
 	static_assert(sizeof(cfg.seq_lut) == sizeof(SEQ_LUT));
 	static_assert(sizeof(cfg.sub_mat) == sizeof(SUB_MAT));
 	static_assert(sizeof(sab_meta) == sizeof(struct meta));
 	memcpy(cfg.seq_lut, SEQ_LUT, sizeof(SEQ_LUT));
 	memcpy(cfg.sub_mat, SUB_MAT, sizeof(SUB_MAT));
+	if (sab_multi_create(&multi, &cfg, 0) != SAB_OK) {
+		perr("%s", sab_multi_last_error(multi));
+		context_release();
+		return nullptr;
+	}
+	atexit(context_release);
+	return multi;
+}
 
-	/* every B200 of the box: one context + host thread per device, disjoint row strips */
-	sab_multi *m = nullptr;
+bool cuda_align(struct input in, struct output out)
+{
+	if (no_cuda)
+		return align(in, out);
+	sab_multi *m = b200_context();
+	if (!m)
+		return false;
 	bool ok = false;
-	if (sab_multi_create(&m, &cfg, 0) != SAB_OK) {
+	if (sab_multi_upload(m, in.seqs, (const sab_meta *)in.meta, in.num, in.max) != SAB_OK) {
 		perr("%s", sab_multi_last_error(m));
 		goto done;
 	}
 	pinfo("Using %d B200 device%s", sab_multi_device_count(m),
 	      sab_multi_device_count(m) == 1 ? "" : "s");
-	if (sab_multi_upload(m, in.seqs, (const sab_meta *)in.meta, in.num, in.max) != SAB_OK) {
-		perr("%s", sab_multi_last_error(m));
-		goto done;
-	}
 
 	pinfo("Performing %zu pairwise alignments", (size_t)alignments((s64)in.num));
 	ppercent(0, "Aligning sequences");
@@ -168,8 +194,7 @@ bool cuda_align(struct input in, struct output out)
 	}
 	ok = true;
 done:
-	sab_multi_destroy(m);
-	return ok;
+	return ok; /* the contexts are released at exit (context_release) */
 }
 
 static void print_backend(void)

@@ -108,6 +108,21 @@ def filter_lost(store, threshold: float) -> np.ndarray:
 
 # --- the real reference binary ----------------------------------------------------------
 
+def ref_binary() -> Path:
+    """The reference build for this host: the reference compiles with -march=native
+    (CMakeLists.txt:7-9); the prebuilt binaries are x86-64-v3 and -v4, take the highest level
+    this CPU runs."""
+    v4 = REF_BIN.with_name("seqalign_v4")
+    if v4.exists():
+        try:
+            flags = next((l for l in open("/proc/cpuinfo") if l.startswith("flags")), "")
+            if all(f" {f}" in flags for f in ("avx512f", "avx512bw", "avx512cd", "avx512dq", "avx512vl")):
+                return v4
+        except OSError:
+            pass
+    return REF_BIN
+
+
 def ref_available() -> bool:
     return REF_BIN.exists() and os.access(REF_BIN, os.X_OK)
 
@@ -126,36 +141,38 @@ def read_raw_dump(path):
     return mat, bool(tri), seqs
 
 
-def ref_args(method: str, matrix: str, gap_pen=None, gap_open=None, gap_ext=None, filter=0.0,
-             **_):
-    args = ["-m", matrix, "-a", method]
-    if gap_pen is not None:
-        args += ["-p", str(gap_pen)]
-    if gap_open is not None:
-        args += ["-s", str(gap_open)]
-    if gap_ext is not None:
-        args += ["-e", str(gap_ext)]
-    if filter and filter > 0:
-        args += ["-f", repr(float(filter))]
-    return args
+def ref_args(*a, **cli):
+    from sequencealigner_b200.synth import cli_args  # the flag spelling lives with the workloads
+    return cli_args(*a, **cli)
 
 
 def run_reference(fasta_path, cli_args, threads: int = 0, write: bool = True, bench: bool = False,
                   binary: Path | None = None, env: dict | None = None):
     """Runs a `seqalign` binary (the reference CPU build by default) on a FASTA file.
     Returns dict(matrix, triangular, seqs, align_seconds, stdout)."""
-    binary = Path(binary or REF_BIN)
+    binary = Path(binary or ref_binary())
     with tempfile.TemporaryDirectory() as td:
         out = Path(td) / "out.bin"
-        cmd = [str(binary), "-i", str(fasta_path), *cli_args, "-F", "-P", "-T", str(threads)]
+        # `-T 0` resolves through omp_get_max_threads() (src/system/os.c:468-473), which obeys
+        # OMP_NUM_THREADS -- torchrun exports OMP_NUM_THREADS=1 -- so "all host threads" is
+        # passed as an explicit count and the OMP_* variables are not inherited.
+        nthreads = threads if threads > 0 else (len(os.sched_getaffinity(0)) or os.cpu_count() or 1)
+        cmd = [str(binary), "-i", str(fasta_path), *cli_args, "-F", "-P", "-T", str(nthreads)]
         cmd += ["-o", str(out)] if write else ["-W"]
         cmd += ["-B"] if bench else ["-Q"]
-        e = dict(os.environ)
+        e = {k: v for k, v in os.environ.items() if not k.startswith(("OMP_", "GOMP_", "KMP_"))}
         e.update(env or {})
         p = subprocess.run(cmd, capture_output=True, text=True, env=e)
         if p.returncode != 0:
             raise RuntimeError(f"reference binary failed ({p.returncode}): {p.stdout}\n{p.stderr}")
-        res = dict(stdout=p.stdout, matrix=None, triangular=None, seqs=None, align_seconds=None)
+        res = dict(stdout=p.stdout, matrix=None, triangular=None, seqs=None, align_seconds=None,
+                   threads=None, filter_seconds=None, binary=binary.name)
+        m = re.search(r"CPU Threads:\s*(\d+)", p.stdout)  # what the reference itself reports
+        if m:
+            res["threads"] = int(m.group(1))
+        m = re.search(r"Filtering:\s*([0-9.]+)\s*sec", p.stdout)
+        if m:
+            res["filter_seconds"] = float(m.group(1))
         if write:
             res["matrix"], res["triangular"], res["seqs"] = read_raw_dump(out)
         if bench:

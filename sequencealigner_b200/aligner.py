@@ -46,6 +46,18 @@ def matrix_lookup(name: str) -> tuple[np.ndarray, np.ndarray]:
     return lut, sub.reshape(24, 24)
 
 
+def filter_resolve(num: int, pairs: np.ndarray) -> np.ndarray:
+    """Phase B of the filter (host only): the sequential recurrence of filter.c:35-55 over the
+    concatenated match lists of all shards.  Returns the lost[] mask."""
+    lib = capi.load()
+    pairs = np.ascontiguousarray(pairs, dtype=np.uint64)
+    lost = np.zeros(num, dtype=np.uint8)
+    rc = lib.sab_filter_resolve(num, pairs.ctypes.data, pairs.size, lost.ctypes.data)
+    if rc < 0:
+        raise capi.SabError(rc, "sab_filter_resolve")
+    return lost.astype(bool)
+
+
 def plan_strips(store: SeqStore, nshards: int = 1, panel: int = 0) -> list[tuple[int, int, int]]:
     """Host-only row-strip plan: (row0, rows, owner shard) per strip -- which rank of a
     multi-GPU job fills which rows of the matrix (no device needed)."""
@@ -186,6 +198,19 @@ class Aligner:
             self._check(rc)
         return lost.astype(bool)
 
+    def filter_matches(self, store: SeqStore, threshold: float, shard: int = 0, nshards: int = 1,
+                       cap: int = 1 << 22) -> np.ndarray:
+        """Phase A of the filter for one shard of the j-tiles: uint64 (j << 32 | i) of every pair
+        whose prefix identity reaches the threshold.  Raises SAB_ERR_OVERFLOW beyond `cap`."""
+        pairs = np.zeros(cap, dtype=np.uint64)
+        count = C.c_int64()
+        seqs = np.ascontiguousarray(store.seqs, dtype=np.uint8)
+        meta = np.ascontiguousarray(store.meta)
+        self._check(self._lib.sab_filter_matches(
+            self._ctx, seqs.ctypes.data, meta.ctypes.data_as(C.POINTER(capi.SabMeta)), store.num,
+            C.c_float(threshold), shard, nshards, pairs.ctypes.data, cap, C.byref(count)))
+        return pairs[:count.value].copy()
+
     def close(self) -> None:
         if self._ctx:
             self._lib.sab_destroy(self._ctx)
@@ -223,8 +248,12 @@ class MultiAligner:
             msg = self._lib.sab_multi_last_error(self._m).decode() if self._m else "sab_multi_create"
             self.close()
             raise capi.SabError(rc, msg)
-        self.ndev = self._lib.sab_multi_device_count(self._m)
         self.num = 0
+
+    @property
+    def ndev(self) -> int:
+        """devices holding the current set (after upload), else the devices requested/available"""
+        return self._lib.sab_multi_device_count(self._m)
 
     def _check(self, rc: int):
         if rc != capi.SAB_OK:
@@ -251,6 +280,18 @@ class MultiAligner:
         self._check(self._lib.sab_multi_align(self._m, ptr, int(triangular),
                                               C.cast(cb, C.c_void_p) if cb else None, None))
         return out
+
+    def filter(self, store: SeqStore, threshold: float) -> np.ndarray:
+        """filter() decisions with phase A spread over the devices (sab_multi_filter)."""
+        lost = np.zeros(store.num, dtype=np.uint8)
+        seqs = np.ascontiguousarray(store.seqs, dtype=np.uint8)
+        meta = np.ascontiguousarray(store.meta)
+        rc = self._lib.sab_multi_filter(self._m, seqs.ctypes.data,
+                                        meta.ctypes.data_as(C.POINTER(capi.SabMeta)), store.num,
+                                        C.c_float(threshold), lost.ctypes.data)
+        if rc < 0:
+            self._check(rc)
+        return lost.astype(bool)
 
     def stats(self) -> dict:
         st = capi.SabStats()

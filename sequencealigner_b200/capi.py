@@ -17,6 +17,10 @@ SAB_FLAG_FORCE_INT32 = 1
 SAB_FLAG_FORCE_INT16 = 2
 SAB_FLAG_STRIP32 = 8
 SAB_FLAG_STRIP16 = 16
+SAB_FLAG_ORDERED = 32
+SAB_FLAG_TEST_RERUN_CAP = 64
+SAB_FLAG_FILTER_SEQUENTIAL = 128
+SAB_FLAG_TEST_FILTER_CAP = 256
 STATUS = {0: "SAB_OK", -1: "SAB_ERR_ARG", -2: "SAB_ERR_NODEVICE", -3: "SAB_ERR_CUDA",
           -4: "SAB_ERR_NOMEM", -5: "SAB_ERR_STATE", -6: "SAB_ERR_OVERFLOW"}
 
@@ -41,7 +45,8 @@ class SabStats(C.Structure):
         ("upload_ms", C.c_double),
         ("pairs", C.c_int64), ("cells", C.c_int64), ("rerun_pairs", C.c_int64),
         ("launches", C.c_int64), ("tiles", C.c_int64), ("tiles_int32", C.c_int64),
-        ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64), ("reserved", C.c_int64 * 3),
+        ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64), ("rerun_strips", C.c_int64),
+        ("filter_matches", C.c_int64), ("filter_ms", C.c_double),
     ]
 
     def as_dict(self):
@@ -54,6 +59,7 @@ PROGRESS_FN = C.CFUNCTYPE(None, C.c_int64, C.c_int64, C.c_void_p)
 SYMBOLS = {
     "sab_abi_version": (C.c_int, []),
     "sab_device_count": (C.c_int, []),
+    "sab_device_ordinal": (C.c_int, [C.c_int]),
     "sab_device_memory": (C.c_int, [C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "sab_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(SabConfig)]),
     "sab_destroy": (None, [C.c_void_p]),
@@ -76,6 +82,12 @@ SYMBOLS = {
     "sab_multi_upload": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(SabMeta), C.c_int32, C.c_int32]),
     "sab_multi_align": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "sab_multi_get_stats": (C.c_int, [C.c_void_p, C.POINTER(SabStats)]),
+    "sab_multi_filter": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(SabMeta), C.c_int32, C.c_float,
+                                   C.c_void_p]),
+    "sab_filter_matches": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(SabMeta), C.c_int32, C.c_float,
+                                     C.c_int32, C.c_int32, C.c_void_p, C.c_int64,
+                                     C.POINTER(C.c_int64)]),
+    "sab_filter_resolve": (C.c_int, [C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
     "sab_filter": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(SabMeta), C.c_int32, C.c_float,
                              C.c_void_p]),
     "sab_matrix_count": (C.c_int, []),

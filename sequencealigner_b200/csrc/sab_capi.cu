@@ -90,8 +90,12 @@ struct sab_ctx {
 	cudaStream_t copy_stream = nullptr;
 	cudaEvent_t ev_copy[2] = { nullptr, nullptr };
 	cudaEvent_t ev_span[2] = { nullptr, nullptr }; // first kernel start / last kernel end
-	int wave_blocks[3][2][2]{}; // [method][packed][narrow] resident persistent blocks
+	int wave_blocks[3][2][2]{}; // [method][packed][narrow] resident persistent blocks, 0 = not set up yet
+	bool sw_prefer_int32 = false; // a strip's re-run list overflowed: later risky strips start in int32
 	sab_stats stats{};
+	// sab_filter.cu keeps its device buffers here (released by sab_destroy)
+	void *filter_state = nullptr;
+	void (*filter_free)(void *) = nullptr;
 };
 
 namespace {
@@ -167,6 +171,26 @@ tile_kernel_t pick_wave_kernel(int method, bool packed, bool narrow)
 int wave_smem_bytes(bool narrow)
 {
 	return narrow ? (int)sizeof(sab::WaveSmem<kStripNarrow>) : (int)sizeof(sab::WaveSmem<kStripWide>);
+}
+
+// Resident persistent blocks of one kernel variant; sets the variant up on first use
+// (dynamic shared memory attribute + occupancy query: ~1 ms each, a job needs one or two).
+int wave_variant(sab_ctx *ctx, int method, bool packed, bool narrow, int *grid)
+{
+	int &slot = ctx->wave_blocks[method][packed][narrow];
+	if (!slot) {
+		int occ = 0;
+		tile_kernel_t wk = pick_wave_kernel(method, packed, narrow);
+		CU(cudaFuncSetAttribute((const void *)wk, cudaFuncAttributeMaxDynamicSharedMemorySize,
+					wave_smem_bytes(narrow)));
+		CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)wk, sab::kWaveThreads,
+								 wave_smem_bytes(narrow)));
+		if (occ < 1)
+			return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
+		slot = occ * ctx->sm_count;
+	}
+	*grid = slot;
+	return SAB_OK;
 }
 
 void free_seqs(sab_ctx *c)
@@ -331,6 +355,25 @@ void lpt_assign(const std::vector<double> &cost, int nshards, std::vector<int> &
 	}
 }
 
+// CUDA ordinals of the devices this library can drive (compute capability 10.x), in ordinal order.
+std::vector<int> usable_devices()
+{
+	std::vector<int> out;
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) {
+		cudaGetLastError();
+		return out;
+	}
+	for (int d = 0; d < n; d++) {
+		int major = 0;
+		if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, d) == cudaSuccess &&
+		    major == 10)
+			out.push_back(d);
+	}
+	cudaGetLastError();
+	return out;
+}
+
 bool int32_safe(const sab_ctx *c, int lq, int ls)
 {
 	int64_t low, high;
@@ -343,6 +386,23 @@ bool int32_safe(const sab_ctx *c, int lq, int ls)
 int sab_internal_device(const sab_ctx *ctx)
 {
 	return ctx && ctx->sm_count ? ctx->cfg.device : -1;
+}
+
+void **sab_internal_filter_slot(sab_ctx *ctx, void (*release)(void *))
+{
+	ctx->filter_free = release;
+	return &ctx->filter_state;
+}
+
+void sab_internal_flags(const sab_ctx *ctx, int *flags)
+{
+	*flags = ctx ? ctx->cfg.flags : 0;
+}
+
+void sab_internal_filter_stats(sab_ctx *ctx, double ms, int64_t matches)
+{
+	ctx->stats.filter_ms = ms;
+	ctx->stats.filter_matches = matches;
 }
 
 int sab_internal_fail(sab_ctx *ctx, int code, const char *fmt, ...)
@@ -366,18 +426,13 @@ int sab_abi_version(void)
 
 int sab_device_count(void)
 {
-	int n = 0;
-	if (cudaGetDeviceCount(&n) != cudaSuccess) {
-		cudaGetLastError();
-		return 0;
-	}
-	int usable = 0;
-	for (int d = 0; d < n; d++) {
-		cudaDeviceProp p;
-		if (cudaGetDeviceProperties(&p, d) == cudaSuccess && p.major == 10)
-			usable++;
-	}
-	return usable;
+	return (int)usable_devices().size();
+}
+
+int sab_device_ordinal(int index)
+{
+	const std::vector<int> dev = usable_devices();
+	return index >= 0 && index < (int)dev.size() ? dev[index] : SAB_ERR_NODEVICE;
 }
 
 int sab_device_memory(int device, size_t *free_bytes, size_t *total_bytes)
@@ -420,6 +475,17 @@ int sab_create(sab_ctx **out, const sab_config *cfg)
 		return fail(ctx, SAB_ERR_ARG, "gap values must be stored <= 0 (align.c:127)");
 	if (cfg->panel < 0 || cfg->panel % kPanelQuantum)
 		return fail(ctx, SAB_ERR_ARG, "panel must be a multiple of %d", kPanelQuantum);
+	// Gotoh with |extend| >= |open| IS Needleman-Wunsch with g = open: M >= X in every cell
+	// (ga.c:61-63), so X = max(Mleft + o, Xleft + e) always takes its first term when e <= o,
+	// and the border recurrence (ga.c:26-37) gives M[0][c] = c*o, not o + (c-1)e.  The strip
+	// kernel's constant GA border only holds for |e| <= |o|, so such configurations (legal on
+	// the CLI: align.c puts no constraint on -s versus -e; equal values are what validate_ga,
+	// ga.c:70-88, offers to switch) run as NW -- exact, and a third of the alu work.
+	if (cfg->method == SAB_GA && cfg->gap_ext <= cfg->gap_open) {
+		ctx->cfg.method = SAB_NW;
+		ctx->cfg.gap_pen = cfg->gap_open;
+		cfg = &ctx->cfg;
+	}
 	ctx->gapA = cfg->method == SAB_NW ? cfg->gap_pen : cfg->gap_open;
 	ctx->gapE = cfg->method == SAB_NW ? 0 : cfg->gap_ext;
 	// symmetric tables only (all 67 reference tables are; the kernels swap the
@@ -453,39 +519,26 @@ int sab_create(sab_ctx **out, const sab_config *cfg)
 	if (cfg->device < 0 || cfg->device >= ndev)
 		return fail(ctx, SAB_ERR_NODEVICE, "device %d out of range (%d present)", cfg->device,
 			    ndev);
-	cudaDeviceProp prop;
-	CU(cudaGetDeviceProperties(&prop, cfg->device));
-	if (prop.major != 10)
+	int major = 0, minor = 0, sms = 0;
+	CU(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, cfg->device));
+	CU(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, cfg->device));
+	CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device));
+	if (major != 10)
 		return fail(ctx, SAB_ERR_NODEVICE,
 			    "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device,
-			    prop.major, prop.minor);
+			    major, minor);
 	CU(cudaSetDevice(cfg->device));
-	ctx->sm_count = prop.multiProcessorCount;
+	ctx->sm_count = sms;
 	CU(cudaMalloc(&ctx->d_sub25, sizeof ctx->sub25));
 	CU(cudaMemcpy(ctx->d_sub25, ctx->sub25, sizeof ctx->sub25, cudaMemcpyHostToDevice));
-	for (int m = 0; m < 3; m++)
-		for (int pk = 0; pk < 2; pk++) {
-			for (int nr = 0; nr < 2; nr++) {
-				int occ = 0;
-				tile_kernel_t wk = pick_wave_kernel(m, pk, nr);
-				CU(cudaFuncSetAttribute((const void *)wk,
-							cudaFuncAttributeMaxDynamicSharedMemorySize,
-							wave_smem_bytes(nr)));
-				CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-					&occ, (const void *)wk, sab::kWaveThreads, wave_smem_bytes(nr)));
-				if (occ < 1)
-					return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
-				ctx->wave_blocks[m][pk][nr] = occ * ctx->sm_count;
-			}
-		}
+	// Kernel variants are set up on first use (wave_variant): a job runs one or two of the twelve.
+	// The pinned bounce buffers and the SW re-run list are allocated on first use as well.
 	for (int i = 0; i < 2; i++) {
 		StripBuf &b = ctx->buf[i];
 		CU(cudaStreamCreateWithFlags(&b.stream, cudaStreamNonBlocking));
 		CU(cudaEventCreate(&b.ev_start));
 		CU(cudaEventCreate(&b.ev_done));
 		CU(cudaMalloc(&b.counter, 4 * sizeof(unsigned)));
-		CU(cudaMalloc(&b.rerun_list, sizeof(unsigned long long) * kRerunCap));
-		CU(cudaHostAlloc(&ctx->stage[i], kStageBytes, cudaHostAllocDefault));
 		CU(cudaEventCreateWithFlags(&ctx->ev_copy[i], cudaEventDisableTiming));
 	}
 	CU(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
@@ -501,6 +554,8 @@ void sab_destroy(sab_ctx *ctx)
 	if (ctx->sm_count) {
 		cudaSetDevice(ctx->cfg.device);
 		cudaDeviceSynchronize();
+		if (ctx->filter_state && ctx->filter_free)
+			ctx->filter_free(ctx->filter_state);
 		free_seqs(ctx);
 		free_bufs(ctx);
 		cudaFree(ctx->d_sub25);
@@ -735,6 +790,9 @@ int drain_strip(sab_ctx *ctx, const Strip &st, StripBuf &b, int32_t *matrix, int
 	const int64_t N = ctx->num;
 	const int64_t a0 = st.a0, a1 = st.a0 + st.an;
 	const size_t stage_elems = kStageBytes / sizeof(int32_t);
+	for (int i = 0; i < 2; i++) // first write-back of this context (-W never gets here)
+		if (!ctx->stage[i])
+			CU(cudaHostAlloc(&ctx->stage[i], kStageBytes, cudaHostAllocDefault));
 	// pass 0 = lower rows (blk), pass 1 = mirror (blkT); two chunks in flight.
 	int slot = 0;
 	bool pending[2] = { false, false };
@@ -819,61 +877,74 @@ int drain_strip(sab_ctx *ctx, const Strip &st, StripBuf &b, int32_t *matrix, int
 
 } // namespace
 
-int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matrix, int triangular,
-		    sab_progress_fn progress, void *user)
+namespace {
+
+// Where a device gets its next row strip from: `order` lists strip indices in issue order and
+// `cursor` hands them out -- private to one shard of the static plan (sab_align_shard), or shared
+// by the devices of one process (sab_multi_align: the "shared atomic tile cursor" of SURVEY 8e, so
+// a device that finishes early simply takes more strips).
+struct StripSource {
+	const std::vector<int> *order;
+	std::atomic<int> *cursor;
+	int next()
+	{
+		const int k = cursor->fetch_add(1);
+		return k < (int)order->size() ? (*order)[k] : -1;
+	}
+};
+
+// Issue order of a set of strips: costliest first (the tail of the job is then made of the cheap
+// ones), or ascending rows under SAB_FLAG_ORDERED (ascending offsets of a file-backed matrix).
+void issue_order(const sab_ctx *ctx, const std::vector<Strip> &strips, std::vector<int> &order)
 {
-	if (!ctx)
-		return SAB_ERR_ARG;
-	if (!ctx->uploaded)
-		return fail(ctx, SAB_ERR_STATE, "sab_upload must precede sab_align");
-	if (nshards < 1 || shard < 0 || shard >= nshards)
-		return fail(ctx, SAB_ERR_ARG, "bad shard %d of %d", shard, nshards);
+	if (ctx->cfg.flags & SAB_FLAG_ORDERED) {
+		std::sort(order.begin(), order.end());
+		return;
+	}
+	std::stable_sort(order.begin(), order.end(),
+			 [&](int x, int y) { return strips[x].cost > strips[y].cost; });
+}
+
+int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &src, int64_t pairs_total,
+		 int32_t *matrix, int triangular, sab_progress_fn progress, void *user)
+{
 	CU(cudaSetDevice(ctx->cfg.device));
 	const double t0 = now_ms();
 	const int num = ctx->num;
 	const int method = ctx->cfg.method;
-	std::vector<Strip> strips;
-	std::vector<int> owner, mine;
-	plan_strips(ctx, nshards, strips, owner);
-	{ // costliest strips first: the tail of the job is then made of the cheap ones
-		std::vector<int> order(strips.size());
-		std::iota(order.begin(), order.end(), 0);
-		std::stable_sort(order.begin(), order.end(),
-				 [&](int x, int y) { return strips[x].cost > strips[y].cost; });
-		for (int idx : order)
-			if (owner[idx] == shard)
-				mine.push_back(idx);
-	}
-	int64_t pairs_total = 0;
-	for (int idx : mine)
-		pairs_total += tri(strips[idx].a0 + strips[idx].an) - tri(strips[idx].a0);
+	std::vector<int> mine; // the strips this call ended up computing
 
 	sab_stats &S = ctx->stats;
-	const double up_ms = S.upload_ms;
-	const int64_t h2d = S.h2d_bytes;
+	const double up_ms = S.upload_ms, flt_ms = S.filter_ms;
+	const int64_t h2d = S.h2d_bytes, flt_m = S.filter_matches;
 	memset(&S, 0, sizeof S);
 	S.upload_ms = up_ms;
 	S.h2d_bytes = h2d;
+	S.filter_ms = flt_ms;
+	S.filter_matches = flt_m;
 
 	DeviceSeqs dseqs{ ctx->d_slot_len, ctx->d_slot_orig, ctx->d_col_off, ctx->d_col_bytes,
 			  ctx->d_grp_off, ctx->d_rowpack };
 	const int bnd_rows = (ctx->max_len + 8 + 3) / 4 * 4;
 	int64_t pairs_done = 0;
 	std::vector<std::pair<float, float>> spans; // kernel intervals on the device timeline
+	const bool test_cap = ctx->cfg.flags & SAB_FLAG_TEST_RERUN_CAP;
+	const unsigned rerun_cap = test_cap ? 4u : kRerunCap;
 
 	auto launch = [&](const Strip &st, StripBuf &b) -> int {
 		const bool packed = st.packed;
 		const bool narrow = st.narrow;
-		const int grid = ctx->wave_blocks[method][packed][narrow];
+		int grid = 0;
+		int rc = wave_variant(ctx, method, packed, narrow, &grid);
+		if (rc)
+			return rc;
 		const int a1 = st.a0 + st.an;
 		const size_t blk_elems = (size_t)(tri(a1) - tri(st.a0));
-		int rc = ensure(ctx, (void **)&b.blk, &b.blk_cap, std::max<size_t>(blk_elems, 1),
-				sizeof(int32_t));
+		rc = ensure(ctx, (void **)&b.blk, &b.blk_cap, std::max<size_t>(blk_elems, 1), sizeof(int32_t));
 		if (rc)
 			return rc;
 		if (!triangular && matrix) {
-			rc = ensure(ctx, (void **)&b.blkT, &b.blkT_cap, (size_t)a1 * st.an,
-				    sizeof(int32_t));
+			rc = ensure(ctx, (void **)&b.blkT, &b.blkT_cap, (size_t)a1 * st.an, sizeof(int32_t));
 			if (rc)
 				return rc;
 		}
@@ -881,6 +952,8 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		rc = ensure(ctx, (void **)&b.bnd, &b.bnd_cap, bnd_block * grid, sizeof(uint2));
 		if (rc)
 			return rc;
+		if (method == SAB_SW && packed && !b.rerun_list)
+			CU(cudaMalloc(&b.rerun_list, sizeof(unsigned long long) * kRerunCap));
 		TileParams p{};
 		p.seqs = dseqs;
 		p.a_slot0 = st.a0;
@@ -893,8 +966,8 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		// short subjects get more of them per item: aim at >= 24 rounds (4 strips each).
 		{
 			const int width = narrow ? kStripNarrow : kStripWide;
-			const int strips = std::max(1, (int)((st.mean_ls + width - 1) / width));
-			const int mult = std::min(8, std::max(1, (24 + 2 * strips - 1) / (2 * strips)));
+			const int nstrips = std::max(1, (int)((st.mean_ls + width - 1) / width));
+			const int mult = std::min(8, std::max(1, (24 + 2 * nstrips - 1) / (2 * nstrips)));
 			p.chunk = (packed ? 16 : 8) * mult;
 		}
 		p.nsc = (a1 + p.chunk - 1) / p.chunk;
@@ -910,7 +983,7 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		p.ovf_threshold = 32767 - std::max(ctx->max_s, 0);
 		p.rerun_list = b.rerun_list;
 		p.rerun_count = b.counter + 1;
-		p.rerun_cap = kRerunCap;
+		p.rerun_cap = rerun_cap;
 		CU(cudaMemsetAsync(b.counter, 0, 4 * sizeof(unsigned), b.stream));
 		if (S.launches == 0)
 			CU(cudaEventRecord(ctx->ev_span[0], b.stream));
@@ -931,17 +1004,27 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		float t_s = 0.f, t_e = 0.f;
 		CU(cudaEventElapsedTime(&t_s, ctx->ev_span[0], b.ev_start));
 		CU(cudaEventElapsedTime(&t_e, ctx->ev_span[0], b.ev_done));
+		const int64_t np = tri(st.a0 + st.an) - tri(st.a0);
 		if (method == SAB_SW && st.packed) {
 			unsigned cnt = 0;
-			CU(cudaMemcpyAsync(&cnt, b.counter + 1, sizeof cnt, cudaMemcpyDeviceToHost,
-					   b.stream));
+			CU(cudaMemcpyAsync(&cnt, b.counter + 1, sizeof cnt, cudaMemcpyDeviceToHost, b.stream));
 			CU(cudaStreamSynchronize(b.stream));
-			if (cnt > kRerunCap)
-				return fail(ctx, SAB_ERR_OVERFLOW,
-					    "int16 re-run list overflowed (%u pairs); use "
-					    "SAB_FLAG_FORCE_INT32",
-					    cnt);
-			if (cnt) {
+			// The per-pair re-run (one thread per pair, rows in global scratch) is for the odd
+			// overflowing pair.  When the list overflowed, or holds more than ~2 % of the strip
+			// (break-even against the int32 instantiation of the strip kernel, which runs at
+			// roughly half the packed rate), the whole strip is swept again in int32 instead.
+			const bool whole = cnt > rerun_cap || (!test_cap && (int64_t)cnt > std::max<int64_t>(4096, np / 50));
+			if (whole) {
+				Strip st32 = st;
+				st32.packed = false;
+				ctx->sw_prefer_int32 = true; // later strips that can overflow start in int32
+				int rc = launch(st32, b);
+				if (rc)
+					return rc;
+				CU(cudaEventSynchronize(b.ev_done));
+				CU(cudaEventElapsedTime(&t_e, ctx->ev_span[0], b.ev_done));
+				S.rerun_strips++;
+			} else if (cnt) {
 				const int cols = ctx->max_len + 1;
 				int rc = ensure(ctx, (void **)&b.rerun_scratch, &b.rerun_scratch_cap,
 						(size_t)kRerunThreads * 2 * cols, sizeof(int32_t));
@@ -951,7 +1034,7 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 				rp.seqs = dseqs;
 				rp.list = b.rerun_list;
 				rp.count = b.counter + 1;
-				rp.cap = kRerunCap;
+				rp.cap = rerun_cap;
 				rp.scratch = b.rerun_scratch;
 				rp.scratch_cols = cols;
 				rp.sub25 = ctx->d_sub25;
@@ -977,8 +1060,6 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 			if (rc)
 				return rc;
 		}
-		const int a1 = st.a0 + st.an;
-		const int64_t np = tri(a1) - tri(st.a0);
 		pairs_done += np;
 		S.pairs += np;
 		if (progress)
@@ -986,22 +1067,33 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 		return SAB_OK;
 	};
 
-	for (size_t k = 0; k < mine.size(); k++) {
-		int rc = launch(strips[mine[k]], ctx->buf[k & 1]);
-		if (rc)
-			return rc;
-		if (k > 0) {
-			rc = finish(strips[mine[k - 1]], ctx->buf[(k - 1) & 1]);
+	// two strips in flight: strip k+1 computes while strip k is re-run / copied back
+	Strip inflight[2];
+	for (int k = 0, prev = -1;; k++) {
+		const int idx = src.next();
+		if (idx >= 0) {
+			Strip &st = inflight[k & 1];
+			st = strips[idx];
+			// once a strip of this job had to be swept again in int32, strips that can overflow
+			// as well (min(lq, ls) * max(S) above the threshold) skip the packed attempt
+			if (method == SAB_SW && st.packed && ctx->sw_prefer_int32 &&
+			    (int64_t)std::min(st.lq, st.ls) * std::max(ctx->max_s, 0) > 32767 - std::max(ctx->max_s, 0))
+				st.packed = false;
+			int rc = launch(st, ctx->buf[k & 1]);
+			if (rc)
+				return rc;
+			mine.push_back(idx);
+		}
+		if (prev >= 0) {
+			int rc = finish(inflight[(k - 1) & 1], ctx->buf[(k - 1) & 1]);
 			if (rc)
 				return rc;
 		}
+		prev = idx;
+		if (idx < 0)
+			break;
 	}
-	if (!mine.empty()) {
-		int rc = finish(strips[mine.back()], ctx->buf[(mine.size() - 1) & 1]);
-		if (rc)
-			return rc;
-	}
-	// exact cell count of this shard: sum over its strips of sum_{hi} len_hi * (sum_{lo<hi} len_lo)
+	// exact cell count of this call: sum over its strips of sum_{hi} len_hi * (sum_{lo<hi} len_lo)
 	{
 		std::vector<int32_t> len_orig(num);
 		for (int s = 0; s < num; s++)
@@ -1043,6 +1135,32 @@ int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matri
 	}
 	S.total_ms = now_ms() - t0;
 	return SAB_OK;
+}
+
+} // namespace
+
+int sab_align_shard(sab_ctx *ctx, int32_t shard, int32_t nshards, int32_t *matrix, int triangular,
+		    sab_progress_fn progress, void *user)
+{
+	if (!ctx)
+		return SAB_ERR_ARG;
+	if (!ctx->uploaded)
+		return fail(ctx, SAB_ERR_STATE, "sab_upload must precede sab_align");
+	if (nshards < 1 || shard < 0 || shard >= nshards)
+		return fail(ctx, SAB_ERR_ARG, "bad shard %d of %d", shard, nshards);
+	std::vector<Strip> strips;
+	std::vector<int> owner, mine;
+	plan_strips(ctx, nshards, strips, owner);
+	for (int idx = 0; idx < (int)strips.size(); idx++)
+		if (owner[idx] == shard)
+			mine.push_back(idx);
+	issue_order(ctx, strips, mine);
+	int64_t pairs_total = 0;
+	for (int idx : mine)
+		pairs_total += tri(strips[idx].a0 + strips[idx].an) - tri(strips[idx].a0);
+	std::atomic<int> cursor{ 0 };
+	StripSource src{ &mine, &cursor };
+	return align_strips(ctx, strips, src, pairs_total, matrix, triangular, progress, user);
 }
 
 int sab_align(sab_ctx *ctx, int32_t *matrix, int triangular, sab_progress_fn progress, void *user)
@@ -1119,14 +1237,23 @@ int sab_get_stats(const sab_ctx *ctx, sab_stats *out)
 
 // ---------------------------------------------------------------------------------------
 // All GPUs of the box from ONE host process: one context + one host thread per device,
-// every device holds a replica of the sequence set and computes its own shard of row
-// strips straight into the caller's matrix (disjoint rows -> no locking, no collective).
-// This is what the reference-signature shim (integration/seqalign_shim.c) drives.
+// every device holds a replica of the sequence set and pulls row strips from a cursor shared
+// by the devices (costliest first), writing them straight into the caller's matrix (disjoint
+// rows -> no locking, no collective).  This is what the reference-signature shim
+// (integration/seqalign_shim.c) drives.
+//
+// Contexts are created lazily and in parallel, and only as many as the job can keep busy: a CUDA
+// context costs a few hundred ms of host time, a C2-sized job (4.5e12 cells) takes 0.5 s on one
+// device (round 1: the drop-in CLI took 1.7 s with one visible device and 5.2 s with eight).
 // ---------------------------------------------------------------------------------------
 #include <mutex>
 
 struct sab_multi {
-	std::vector<sab_ctx *> ctx;
+	sab_config cfg{};
+	std::vector<int> ordinals; // usable CUDA ordinals this object may drive
+	int want = 0; // devices the caller asked for (0 = size from the job)
+	std::vector<sab_ctx *> ctx; // created so far, ctx[k] drives ordinals[k]
+	int active = 0; // contexts holding the current sequence set
 	std::string err;
 	sab_stats stats{};
 	// progress aggregation
@@ -1157,21 +1284,71 @@ void multi_progress(int64_t done, int64_t, void *user)
 		m->progress(sum, m->total, m->user);
 }
 
-template <typename F> int multi_run(sab_multi *m, F fn)
+template <typename F> int multi_run(sab_multi *m, int n, F fn)
 {
-	const int n = (int)m->ctx.size();
 	std::vector<int> rc(n, SAB_OK);
-	std::vector<std::thread> th;
-	for (int k = 0; k < n; k++)
-		th.emplace_back([&, k]() { rc[k] = fn(k); });
-	for (auto &t : th)
-		t.join();
+	if (n == 1) {
+		rc[0] = fn(0);
+	} else {
+		std::vector<std::thread> th;
+		for (int k = 0; k < n; k++)
+			th.emplace_back([&, k]() { rc[k] = fn(k); });
+		for (auto &t : th)
+			t.join();
+	}
 	for (int k = 0; k < n; k++)
 		if (rc[k] != SAB_OK) {
-			m->err = "device " + std::to_string(k) + ": " + sab_last_error(m->ctx[k]);
+			m->err = "device " + std::to_string(m->ordinals[k]) + ": " +
+				 (k < (int)m->ctx.size() && m->ctx[k] ? sab_last_error(m->ctx[k]) : "no context");
 			return rc[k];
 		}
 	return SAB_OK;
+}
+
+// Makes sure contexts [0, n) exist; the missing ones are created concurrently.
+int multi_ensure(sab_multi *m, int n)
+{
+	const int have = (int)m->ctx.size();
+	if (n <= have)
+		return SAB_OK;
+	m->ctx.resize(n, nullptr);
+	std::vector<int> rc(n, SAB_OK);
+	std::vector<std::thread> th;
+	auto make = [&](int k) {
+		sab_config c = m->cfg;
+		c.device = m->ordinals[k];
+		c.shards_hint = std::max(m->want, (int)m->ordinals.size());
+		rc[k] = sab_create(&m->ctx[k], &c);
+	};
+	if (n - have == 1) {
+		make(have);
+	} else {
+		for (int k = have; k < n; k++)
+			th.emplace_back(make, k);
+		for (auto &t : th)
+			t.join();
+	}
+	for (int k = have; k < n; k++)
+		if (rc[k] != SAB_OK) {
+			m->err = "device " + std::to_string(m->ordinals[k]) + ": " + sab_last_error(m->ctx[k]);
+			const int code = rc[k];
+			for (int j = have; j < n; j++)
+				sab_destroy(m->ctx[j]);
+			m->ctx.resize(have);
+			return code;
+		}
+	m->done.assign(n, 0);
+	return SAB_OK;
+}
+
+// Devices worth starting for `seconds` of single-device work: each one should get at least
+// ~0.4 s of it (what creating its context and replicating the sequence set costs the host).
+int devices_for(const sab_multi *m, double seconds)
+{
+	const int cap = (int)m->ordinals.size();
+	if (m->want > 0)
+		return std::min(m->want, cap);
+	return std::max(1, std::min(cap, (int)(seconds / 0.4)));
 }
 
 } // namespace
@@ -1187,36 +1364,28 @@ int sab_multi_create(sab_multi **out, const sab_config *cfg, int32_t ndev)
 	if (!m)
 		return SAB_ERR_NOMEM;
 	*out = m;
-	const int have = sab_device_count();
-	if (ndev <= 0)
-		ndev = have;
+	m->cfg = *cfg;
+	m->ordinals = usable_devices();
+	const int have = (int)m->ordinals.size();
 	if (have == 0 || ndev > have) {
 		m->err = have ? "more devices requested than present" :
 				"no CUDA device (this library has no CPU fallback)";
 		return SAB_ERR_NODEVICE;
 	}
-	for (int k = 0; k < ndev; k++) {
-		sab_config c = *cfg;
-		c.device = k;
-		c.shards_hint = ndev;
-		sab_ctx *ctx = nullptr;
-		const int rc = sab_create(&ctx, &c);
-		m->ctx.push_back(ctx);
-		if (rc != SAB_OK) {
-			m->err = "device " + std::to_string(k) + ": " + sab_last_error(ctx);
-			return rc;
-		}
-	}
-	m->done.assign(ndev, 0);
-	return SAB_OK;
+	m->want = ndev > 0 ? ndev : 0;
+	// validate the configuration now (sab_create's argument checks), on the first device
+	return multi_ensure(m, 1);
 }
 
 void sab_multi_destroy(sab_multi *m)
 {
 	if (!m)
 		return;
+	std::vector<std::thread> th; // context teardown is as slow as creation: in parallel too
 	for (sab_ctx *c : m->ctx)
-		sab_destroy(c);
+		th.emplace_back([c]() { sab_destroy(c); });
+	for (auto &t : th)
+		t.join();
 	delete m;
 }
 
@@ -1227,31 +1396,65 @@ const char *sab_multi_last_error(const sab_multi *m)
 
 int sab_multi_device_count(const sab_multi *m)
 {
-	return m ? (int)m->ctx.size() : 0;
+	if (!m)
+		return 0;
+	return m->active ? m->active : (m->want ? m->want : (int)m->ordinals.size());
 }
 
 int sab_multi_upload(sab_multi *m, const uint8_t *seqs, const sab_meta *meta, int32_t num, int32_t max)
 {
-	if (!m || m->ctx.empty())
+	if (!m || m->ctx.empty() || !meta || num < 2)
 		return SAB_ERR_ARG;
-	return multi_run(m, [&](int k) { return sab_upload(m->ctx[k], seqs, meta, num, max); });
+	// size the device set from the job: cells / ~6 TCUPS per device
+	double sum = 0, sq = 0;
+	for (int32_t k = 0; k < num; k++) {
+		sum += meta[k].len;
+		sq += (double)meta[k].len * meta[k].len;
+	}
+	const int n = devices_for(m, (sum * sum - sq) / 2 / 6e12);
+	int rc = multi_ensure(m, n);
+	if (rc)
+		return rc;
+	m->active = 0;
+	rc = multi_run(m, n, [&](int k) {
+		// the auto panel is sized for the devices that take part in THIS job
+		m->ctx[k]->cfg.shards_hint = n;
+		return sab_upload(m->ctx[k], seqs, meta, num, max);
+	});
+	if (rc == SAB_OK)
+		m->active = n;
+	return rc;
 }
 
 int sab_multi_align(sab_multi *m, int32_t *matrix, int triangular, sab_progress_fn progress, void *user)
 {
 	if (!m || m->ctx.empty())
 		return SAB_ERR_ARG;
-	const int n = (int)m->ctx.size();
+	const int n = m->active;
+	if (n < 1) {
+		m->err = "sab_multi_upload must precede sab_multi_align";
+		return SAB_ERR_STATE;
+	}
 	m->progress = progress;
 	m->user = user;
-	std::fill(m->done.begin(), m->done.end(), 0);
-	m->total = m->ctx[0]->uploaded ? tri(m->ctx[0]->num) : 0;
+	m->done.assign(n, 0);
+	m->total = tri(m->ctx[0]->num);
 	std::vector<MultiSlot> slots(n);
 	for (int k = 0; k < n; k++)
 		slots[k] = { m, k };
+	// one plan (every context holds the same set and panel), one cursor: dynamic balancing
+	std::vector<Strip> strips;
+	std::vector<int> owner, order;
+	plan_strips(m->ctx[0], 1, strips, owner);
+	order.resize(strips.size());
+	std::iota(order.begin(), order.end(), 0);
+	issue_order(m->ctx[0], strips, order);
+	std::atomic<int> cursor{ 0 };
 	const double t0 = now_ms();
-	const int rc = multi_run(m, [&](int k) {
-		return sab_align_shard(m->ctx[k], k, n, matrix, triangular, multi_progress, &slots[k]);
+	const int rc = multi_run(m, n, [&](int k) {
+		StripSource src{ &order, &cursor };
+		return align_strips(m->ctx[k], strips, src, m->total, matrix, triangular, multi_progress,
+				    &slots[k]);
 	});
 	if (rc != SAB_OK)
 		return rc;
@@ -1265,15 +1468,58 @@ int sab_multi_align(sab_multi *m, int32_t *matrix, int triangular, sab_progress_
 		S.pairs += s.pairs;
 		S.cells += s.cells;
 		S.rerun_pairs += s.rerun_pairs;
+		S.rerun_strips += s.rerun_strips;
 		S.launches += s.launches;
 		S.tiles += s.tiles;
 		S.tiles_int32 += s.tiles_int32;
 		S.h2d_bytes += s.h2d_bytes;
 		S.d2h_bytes += s.d2h_bytes;
 	}
+	S.filter_ms = m->stats.filter_ms;
+	S.filter_matches = m->stats.filter_matches;
 	S.total_ms = now_ms() - t0;
 	m->stats = S;
 	return SAB_OK;
+}
+
+int sab_multi_filter(sab_multi *m, const uint8_t *seqs, const sab_meta *meta, int32_t num,
+		     float threshold, uint8_t *lost)
+{
+	if (!m || m->ctx.empty() || !seqs || !meta || !lost || num < 1)
+		return SAB_ERR_ARG;
+	const double t0 = now_ms();
+	// ~1.5e11 prefix compares per second and device (the kernel stops a pair as soon as the
+	// threshold is out of reach; C4: 5e9 pairs)
+	const int n = devices_for(m, (double)num * (num - 1) / 2 / 1.5e11);
+	int rc = multi_ensure(m, n);
+	if (rc)
+		return rc;
+	std::vector<std::vector<uint64_t>> part(n);
+	std::vector<int> overflow(n, 0);
+	rc = multi_run(m, n, [&](int k) {
+		return sab_internal_filter_matches(m->ctx[k], seqs, meta, num, threshold, k, n, part[k],
+						   &overflow[k]);
+	});
+	if (rc != SAB_OK)
+		return rc;
+	int nlost;
+	if (std::any_of(overflow.begin(), overflow.end(), [](int o) { return o != 0; })) {
+		// too many matching pairs to list (a threshold most pairs pass): the exact
+		// panel-sequential path on one device
+		nlost = sab_filter(m->ctx[0], seqs, meta, num, threshold, lost);
+		if (nlost < 0) {
+			m->err = sab_last_error(m->ctx[0]);
+			return nlost;
+		}
+	} else {
+		std::vector<uint64_t> all;
+		for (auto &p : part)
+			all.insert(all.end(), p.begin(), p.end());
+		nlost = sab_filter_resolve(num, all.data(), (int64_t)all.size(), lost);
+		m->stats.filter_matches = (int64_t)all.size();
+	}
+	m->stats.filter_ms = now_ms() - t0;
+	return nlost;
 }
 
 int sab_multi_get_stats(const sab_multi *m, sab_stats *out)

@@ -51,6 +51,21 @@ CONFIGS = {
 }
 
 
+def cli_args(method: str, matrix: str, gap_pen=None, gap_open=None, gap_ext=None, filter=0.0,
+             **_) -> list[str]:
+    """The reference CLI's spelling of a workload (src/bio/align.c:111-202, filter.c:103-117)."""
+    args = ["-m", matrix, "-a", method]
+    if gap_pen is not None:
+        args += ["-p", str(gap_pen)]
+    if gap_open is not None:
+        args += ["-s", str(gap_open)]
+    if gap_ext is not None:
+        args += ["-e", str(gap_ext)]
+    if filter and filter > 0:
+        args += ["-f", repr(float(filter))]
+    return args
+
+
 def make(config: str, n: int | None = None, seed: int | None = None) -> tuple[SeqStore, dict]:
     cfg = dict(CONFIGS[config])
     if n is not None:

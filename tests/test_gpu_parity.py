@@ -324,3 +324,156 @@ def test_long_sequences_beyond_the_reference_cuda_cap(oracle_mod, method, kw):
     assert np.array_equal(got, want)
     if method == "nw":
         assert st["tiles_int32"] > 0
+
+
+# ---- round 2 ---------------------------------------------------------------------------
+
+@pytest.mark.parametrize("method", ["ga", "sw"])
+@pytest.mark.parametrize("gaps", [(2, 5), (0, 1), (3, 3), (0, 0), (1, 30)])
+@pytest.mark.parametrize("flags", [0, capi.SAB_FLAG_FORCE_INT32])
+def test_gap_extend_dearer_than_open(oracle_mod, method, gaps, flags):
+    """-s below -e is legal on the CLI (align.c puts no constraint on them).  Gotoh then
+    degenerates to NW with g = open (the border recurrence ga.c:26-37 gives c*o, not o+(c-1)e):
+    the library routes it; SW keeps the general cell.  Oracle = the GA/SW recurrences as written."""
+    rng = np.random.default_rng(23)
+    lens = np.concatenate([rng.integers(1, 200, size=300), [1, 2, 31, 32, 33, 64, 65]])
+    store = SeqStore.from_codes(rng.integers(0, 20, size=int(lens.sum())), lens, synth.PROTEIN20)
+    cfg = AlignConfig(method, "blosum62", gap_open=gaps[0], gap_ext=gaps[1])
+    r = cfg.resolve()
+    if gaps[0] != gaps[1]:
+        assert r["method"] == (capi.SAB_GA if method == "ga" else capi.SAB_SW)  # oracle sees GA/SW
+    want, _ = oracle_mod.align_all(r, store, triangular=True)
+    got, _ = gpu_scores(cfg, store, triangular=True, panel=128, flags=flags)
+    bad = np.flatnonzero(got != want)
+    assert bad.size == 0, (bad[:10], got[bad[:10]], want[bad[:10]])
+
+
+def test_sw_rerun_list_overflow_resweeps_the_strip_in_int32(oracle_mod):
+    """more overflowing pairs than the int16 re-run list holds (cap lowered to 4 by the test
+    flag): the strip is swept again by the int32 instantiation instead of failing"""
+    store, c = synth.make_overflow(n=300, planted=8)
+    cfg = AlignConfig("sw", "pam500", gap_open=10, gap_ext=1)
+    want, _ = oracle_mod.align_all(cfg.resolve(), store)
+    for tri in (True, False):
+        got, st = gpu_scores(cfg, store, triangular=tri, panel=128,
+                             flags=capi.SAB_FLAG_TEST_RERUN_CAP | capi.SAB_FLAG_FORCE_INT16)
+        assert st["rerun_strips"] >= 1 and st["tiles_int32"] >= 1
+        if tri:
+            assert np.array_equal(got, want)
+        else:
+            assert np.array_equal(got[np.tril_indices(store.num, -1)], want)
+            assert np.array_equal(got, got.T)
+
+
+def test_sw_many_identical_high_scoring_sequences(oracle_mod):
+    """~1500 identical high-scoring sequences in one panel used to end in
+    SAB_ERR_OVERFLOW.  1500 x poly-W(1000) under pam500: every pair scores 34000 > int16, 1.1e6
+    of them -> more than 2 % of a strip, so strips are swept again in int32, and once that has
+    happened the remaining strips start in int32."""
+    seqs = [b"W" * 1000] * 1500
+    store = SeqStore.from_sequences(seqs)
+    cfg = AlignConfig("sw", "pam500", gap_open=10, gap_ext=1)
+    got, st = gpu_scores(cfg, store, triangular=True)
+    assert 1 <= st["rerun_strips"] < st["tiles"] and st["rerun_pairs"] == 0
+    # every strip ended in int32: swept again after a packed attempt, or started there
+    assert st["tiles_int32"] == st["tiles"] - st["rerun_strips"]
+    assert (got == 34000).all()
+    assert oracle_mod.pair(cfg.resolve(), seqs[5], seqs[0]) == 34000
+
+
+@pytest.mark.parametrize("thr", [0.9, 0.3])
+def test_filter_paths_agree(oracle_mod, thr):
+    """match list (default), panel-sequential (flag), list overflow -> fallback (test cap),
+    sharded phase A + host resolve, and the multi-device entry point: one answer"""
+    from sequencealigner_b200 import MultiAligner
+    from sequencealigner_b200.aligner import filter_resolve
+    store, c = synth.make("c4", n=6000)
+    want = oracle_mod.filter_lost(store, thr)
+    cfg = AlignConfig("ga", "blosum62", gap_open=10, gap_ext=1)
+    for flags in (0, capi.SAB_FLAG_FILTER_SEQUENTIAL, capi.SAB_FLAG_TEST_FILTER_CAP):
+        with Aligner(cfg, flags=flags) as al:
+            got = al.filter(store, thr)
+            st = al.stats()
+        assert np.array_equal(got, want), flags
+        assert st["filter_ms"] > 0
+        assert (st["filter_matches"] >= 0) == (flags == 0)
+    with Aligner(cfg) as al:
+        parts = [al.filter_matches(store, thr, shard=k, nshards=3) for k in range(3)]
+        whole = al.filter_matches(store, thr)
+    assert sorted(np.concatenate(parts).tolist()) == sorted(whole.tolist())
+    assert np.array_equal(filter_resolve(store.num, np.concatenate(parts)), want)
+    with Aligner(cfg) as al, pytest.raises(capi.SabError):
+        al.filter_matches(store, thr, cap=3)
+    with MultiAligner(cfg) as ma:
+        assert np.array_equal(ma.filter(store, thr), want)
+        kept = store.subset(~want)
+        ma.upload(kept)  # the same contexts then run the alignment
+        got = ma.align()
+    ref, _ = oracle_mod.align_all(cfg.resolve(), kept.head(200))
+    assert np.array_equal(got[:ref.size], ref)
+
+
+@pytest.mark.parametrize("flags", [0, capi.SAB_FLAG_ORDERED])
+@pytest.mark.parametrize("tri", [True, False])
+def test_file_backed_map_shared_sink(tmp_path, flags, tri):
+    """f2: the matrix may be a file-backed MAP_SHARED mapping (alloc_mmap, src/system/os.c:103-140):
+    plain stores from the library's threads, bit-equal to the in-RAM result, in both layouts, in
+    cost order and in ascending-row order"""
+    import mmap
+    store, c = synth.make("c1", n=1500)
+    cfg = AlignConfig("ga", "blosum62", gap_open=10, gap_ext=1)
+    n = store.num
+    count = n * (n - 1) // 2 if tri else n * n
+    path = tmp_path / "sink.bin"
+    with open(path, "wb") as f:
+        f.truncate(count * 4)
+    with Aligner(cfg, panel=256, flags=flags) as al:
+        al.upload(store)
+        ram = al.align(triangular=tri)
+        with open(path, "r+b") as f:
+            mm = mmap.mmap(f.fileno(), count * 4, flags=mmap.MAP_SHARED)
+            view = np.frombuffer(mm, dtype=np.int32)
+            al.align(triangular=tri, out=view if tri else view.reshape(n, n))
+            del view
+            mm.flush()
+            mm.close()
+    back = np.fromfile(path, dtype=np.int32)
+    assert np.array_equal(back, ram.reshape(-1))
+
+
+def test_ordered_flag_issues_strips_in_row_order():
+    store, c = synth.make("c1", n=1200)
+    cfg = AlignConfig("nw", "blosum62", gap_pen=4)
+    for flags, check in ((capi.SAB_FLAG_ORDERED, lambda d: d == sorted(d)),
+                         (0, lambda d: d != sorted(d))):
+        done = []
+        with Aligner(cfg, panel=128, flags=flags) as al:
+            al.upload(store)
+            rows = {0: 0}
+            acc = 0
+            for row0, nrows, _ in al.strips():
+                acc += (row0 + nrows) * (row0 + nrows - 1) // 2 - row0 * (row0 - 1) // 2
+            al.align(progress=lambda d, t, u: done.append(d))
+        # progress counts pairs: in row order the increments grow (strip k holds more pairs than k-1)
+        inc = [b - a for a, b in zip([0] + done, done)]
+        assert done[-1] == acc and check(inc[:-1]), (flags, inc)
+
+
+def test_multi_device_dynamic_cursor_every_strip_exactly_once(oracle_mod):
+    """sab_multi_align: the devices pull strips from one shared cursor; whatever the device
+    count, every row strip is computed exactly once (checked against the oracle)"""
+    from sequencealigner_b200 import MultiAligner
+    store, c = synth.make("c1", n=900)
+    cfg = AlignConfig("ga", "blosum62", gap_open=10, gap_ext=1)
+    want, _ = oracle_mod.align_all(cfg.resolve(), store, triangular=True)
+    ndev_all = capi.load().sab_device_count()
+    for ndev in sorted({1, ndev_all}):
+        with MultiAligner(cfg, ndev=ndev, panel=128) as ma:
+            ma.upload(store)
+            assert ma.ndev == ndev
+            out = np.full(want.size, -77, dtype=np.int32)
+            ma.align(out=out)
+            st = ma.stats()
+        assert np.array_equal(out, want)
+        assert st["pairs"] == store.pairs() and st["cells"] == store.cells()
+        assert st["tiles"] == (store.num + 127) // 128

@@ -123,3 +123,27 @@ def test_strip_plan_covers_rows_once_and_balances():
             load[o] += float((lens[a:a + b] * pre[a:a + b]).sum())
         assert load.min() > 0 and load.max() / load.mean() < 1.08
     assert plan_strips(store, 4) == plan_strips(store, 4)  # deterministic on every rank
+
+
+def test_filter_resolve_is_the_sequential_recurrence(oracle_mod):
+    """sab_filter_resolve (host only): fed with every pair that passes the threshold -- computed
+    here with numpy in the reference's float32 arithmetic -- it must reproduce filter.c:35-55."""
+    import numpy as np
+    from sequencealigner_b200 import synth
+    from sequencealigner_b200.aligner import filter_resolve
+    store, _ = synth.make("c4", n=700)
+    seqs = [np.frombuffer(store.sequence(k), dtype=np.uint8) for k in range(store.num)]
+    for thr in (0.9, 0.4, 0.05):
+        pairs = []
+        for j in range(1, store.num):
+            for i in range(j):
+                ml = min(len(seqs[i]), len(seqs[j]))
+                m = int((seqs[i][:ml] == seqs[j][:ml]).sum())
+                if np.float32(m) / np.float32(ml) >= np.float32(thr):
+                    pairs.append((j << 32) | i)
+        rng = np.random.default_rng(1)
+        pairs = np.array(pairs, dtype=np.uint64)
+        rng.shuffle(pairs)  # phase A delivers them in no particular order
+        got = filter_resolve(store.num, pairs)
+        assert np.array_equal(got, oracle_mod.filter_lost(store, thr)), thr
+    assert not filter_resolve(5, np.zeros(0, np.uint64)).any()

@@ -51,9 +51,24 @@ def run(name, seqs, threads=1, **cli):
           f"sum={int(res['matrix'].astype(np.int64).sum())}")
 
 
+def extra():
+    """Fixtures added after round 1; their own generator, so the ones above keep their bytes."""
+    rng = np.random.default_rng(20261105)
+    prot = rand_seqs(rng, 40, 1, 90, P20)
+    # extend dearer than open (legal on the CLI, align.c:111-202): GA degenerates to NW with g = open
+    run("protein_ga_blosum62_s2e5", prot, method="ga", matrix="blosum62", gap_open=2, gap_ext=5)
+    run("protein_ga_blosum62_s0e1", prot, method="ga", matrix="blosum62", gap_open=0, gap_ext=1)
+    run("protein_sw_blosum62_s2e5", prot, method="sw", matrix="blosum62", gap_open=2, gap_ext=5)
+    run("protein_sw_blosum62_s0e1", prot, method="sw", matrix="blosum62", gap_open=0, gap_ext=1)
+    iupac = rand_seqs(rng, 24, 10, 120, N16)
+    run("iupac_ga_dnafull_s3e7", iupac, method="ga", matrix="dnafull", gap_open=3, gap_ext=7)
+
+
 def main():
     assert oracle.ref_available(), "build oracle/_ref/seqalign first (make -C oracle)"
     OUT.mkdir(parents=True, exist_ok=True)
+    if "--extra" in sys.argv:
+        return extra()
     rng = np.random.default_rng(20261104)
     prot = rand_seqs(rng, 48, 1, 70, P20)
     run("protein_nw_blosum62_p4", prot, method="nw", matrix="blosum62", gap_pen=4)
@@ -116,6 +131,7 @@ def main():
     np.savez_compressed(OUT / "all_tables.npz", protein=np.frombuffer(fasta_bytes(small_p), np.uint8),
                         nucleo=np.frombuffer(fasta_bytes(small_n), np.uint8), **allm)
     print(f"all_tables: {len(allm)} matrices")
+    extra()
 
 
 if __name__ == "__main__":
