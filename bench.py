@@ -190,6 +190,27 @@ def cpu_reference_sample(store, c, target_s: float = 15.0):
             "_cells": cells, "_secs": secs, "_m": m}
 
 
+def cpu_reference_filter_sample(store, c, m=20000):
+    """The reference's own CPU filter (src/bio/filter.c, all host threads -- its OpenMP loop races
+    on lost[], so only the time is used) on the first m sequences of the workload."""
+    from oracle import oracle
+    from sequencealigner_b200 import synth
+    if not oracle.ref_available():
+        return None
+    sub = store.head(m)
+    with tempfile.TemporaryDirectory() as td:
+        fa = Path(td) / "sample.fasta"
+        sub.to_fasta(fa)
+        r = oracle.run_reference(fa, synth.cli_args(**c), threads=0, write=False, bench=True)
+    secs = r["filter_seconds"]
+    if not secs:
+        return None
+    return {"seconds": secs, "sequences": sub.num, "pairs_per_s": sub.pairs() / secs,
+            "threads": r["threads"],
+            "sample": f"first {sub.num} of {store.num} sequences, -f {c['filter']}, reference's "
+                      f"'Filtering: X sec' (-B)"}
+
+
 def cli_end_to_end(store, c, binary, threads=0, extra=()):
     """End-to-end pairs/s of a `seqalign` CLI build (BASELINE.json: "end-to-end pairs/sec" =
     pairs / wall time of the whole run: FASTA parse, filter, alignment, HDF5 write)."""
@@ -320,8 +341,12 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_gpus = world
+    # --emulate-shards K: ONE GPU computes shard 0 of K of the K-GPU job (same set, same panels, no
+    # neighbours): attributes per-GPU rate changes between N = 1 and N = K to the plan, not the box
+    emu = args.emulate_shards if world == 1 and args.emulate_shards > 1 else 0
+    nsh, my_shard = (emu, 0) if emu else (world, rank)
 
-    store, cfg, c, desc = workload(args.config, n_gpus, args.n, args.method, args.scaling)
+    store, cfg, c, desc = workload(args.config, emu or n_gpus, args.n, args.method, args.scaling)
     # `config` is kept identical to the reference arm's; what is specific to this arm goes beside it
     parallelism = f"row-strip shards x{n_gpus}, no collective"
     l2_flush = "512 MiB device memset between timed steps"
@@ -333,14 +358,55 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    al = Aligner(cfg, device=local_rank, shards_hint=n_gpus, flags=args.flags, panel=args.panel)
+    al = Aligner(cfg, device=local_rank, shards_hint=nsh, flags=args.flags, panel=args.panel)
+
+    # ---- -f: the redundancy filter runs first, the alignment on the survivors ----
+    filt = None
+    store_in = store  # what the CLI / CPU legs are given (they filter themselves)
+    if c.get("filter") and not args.no_filter:
+        from sequencealigner_b200.aligner import filter_resolve
+        thr = float(c["filter"])
+        n_in = store.num
+
+        def run_filter():
+            if world == 1:
+                return al.filter(store, thr), al.stats()["filter_matches"]
+            # phase A on this rank's share of the j-tiles, the match lists exchanged over NCCL
+            # (the path's one real exchange step), phase B -- sequential -- on every rank alike
+            mine = torch.from_numpy(al.filter_matches(store, thr, shard=rank, nshards=world)
+                                    .view(np.int64)).cuda()
+            cnt = torch.tensor([mine.numel()], dtype=torch.int64, device="cuda")
+            cnts = [torch.zeros_like(cnt) for _ in range(world)]
+            dist.all_gather(cnts, cnt)
+            cap = max(1, max(int(x.item()) for x in cnts))
+            pad = torch.zeros(cap, dtype=torch.int64, device="cuda")
+            pad[:mine.numel()] = mine
+            parts = [torch.zeros_like(pad) for _ in range(world)]
+            dist.all_gather(parts, pad)
+            allp = torch.cat([p_[:int(k.item())] for p_, k in zip(parts, cnts)]).cpu().numpy()
+            return filter_resolve(n_in, allp.view(np.uint64)), int(allp.size)
+
+        run_filter()  # warm-up: device buffers, module load
+        barrier()
+        t_f = time.perf_counter()
+        lost, n_match = run_filter()
+        barrier()
+        f_ms, _ = reduce_over_ranks((time.perf_counter() - t_f) * 1e3, 0)
+        store = store.subset(~lost)
+        filt = {"threshold": thr, "sequences_in": n_in, "sequences_after": store.num,
+                "lost": int(lost.sum()), "pairs_compared": n_in * (n_in - 1) // 2,
+                "matching_pairs": n_match, "ms": f_ms,
+                "pairs_after": store.pairs(), "cells_after": store.cells(),
+                "lost_checksum": int(np.flatnonzero(lost).astype(np.int64).sum()),
+                "what": "sab_filter (1 GPU) / sab_filter_matches per rank + NCCL all_gather + "
+                        "sab_filter_resolve (N GPUs): wall clock incl. packing, H2D, D2H, resolve"}
     al.upload(store)
     n = store.num
     host_matrix = np.zeros(n * (n - 1) // 2, dtype=np.int32)
 
     # ---- device-resident throughput (`value`) ------------------------------------------
     for _ in range(args.warmup):
-        al.align(write=False, shard=rank, nshards=world)
+        al.align(write=False, shard=my_shard, nshards=nsh)
     dev_ms, my_cells, launches = 0.0, 0, 0
     kernel_ms = 0.0
     barrier()
@@ -349,7 +415,7 @@ def run_ours(args):
         for _ in range(args.steps):
             flush.zero_()
             torch.cuda.synchronize()
-            al.align(write=False, shard=rank, nshards=world)
+            al.align(write=False, shard=my_shard, nshards=nsh)
             st = al.stats()
             dev_ms += st["device_ms"]
             kernel_ms += st["kernel_ms"]
@@ -366,7 +432,7 @@ def run_ours(args):
     # ---- end to end through the C ABI with host buffers (`e2e`) ------------------------
     for _ in range(min(args.warmup, 1)):
         al.upload(store)
-        al.align(out=host_matrix, shard=rank, nshards=world)
+        al.align(out=host_matrix, shard=my_shard, nshards=nsh)
     barrier()
     e2e_t0 = time.perf_counter()
     h2d = d2h = 0
@@ -375,7 +441,7 @@ def run_ours(args):
         t_a = time.perf_counter()
         al.upload(store)
         t_b = time.perf_counter()
-        al.align(out=host_matrix, shard=rank, nshards=world)
+        al.align(out=host_matrix, shard=my_shard, nshards=nsh)
         t_c = time.perf_counter()
         st = al.stats()
         h2d, d2h = st["h2d_bytes"], st["d2h_bytes"]
@@ -457,22 +523,25 @@ def run_ours(args):
     cli = None
     dropin = ROOT / "integration" / "_build" / "seqalign_b200"
     if n_gpus == 1 and not args.no_cli and dropin.exists():
-        cli = cli_end_to_end(store, c, dropin)
+        cli = cli_end_to_end(store_in, c, dropin)
 
     cpu = None
     if n_gpus == 1 and not args.no_cpu:
-        cpu = cpu_reference_sample(store, c, target_s=args.cpu_seconds)
+        cpu = cpu_reference_sample(store_in, c, target_s=args.cpu_seconds)
         cpu = {k: v for k, v in cpu.items() if not k.startswith("_")}
+        if filt:
+            cpu["filter"] = cpu_reference_filter_sample(store_in, c)
 
     out = {
         "metric": "all-vs-all GCUPS", "value": value, "unit": "GCUPS", "n_gpus": n_gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms,
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int16x2",
         "data": "synthetic", "config": desc, "parallelism": parallelism, "l2_flush": l2_flush,
-        "pairs_per_s": desc["pairs"] / (step_ms * 1e-3),
+        "pairs_per_s": (filt["pairs_after"] if filt else desc["pairs"]) / (step_ms * 1e-3),
+        "filter": filt, "emulated_shard": (f"0 of {emu}" if emu else None),
         "wall_ms_per_step": wall_ms / args.steps,
         "e2e": {"value": e2e_value, "unit": "GCUPS", "ms_per_step": e2e_ms,
-                "pairs_per_s": desc["pairs"] / (e2e_ms * 1e-3),
+                "pairs_per_s": (filt["pairs_after"] if filt else desc["pairs"]) / (e2e_ms * 1e-3),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "checksum": checksum, "steps_rank0": e2e_steps},
         "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
@@ -497,6 +566,9 @@ def main():
                          "the config's own size at every N (BASELINE.json quotes C3 at 1/2/4/8)")
     ap.add_argument("--method", default=None, choices=["nw", "ga", "sw"],
                     help="override the config's alignment method (informational runs)")
+    ap.add_argument("--emulate-shards", type=int, default=0,
+                    help="one GPU computes shard 0 of K of the K-GPU job (attribution runs)")
+    ap.add_argument("--no-filter", action="store_true", help="skip the -f leg of configs that have one")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-cli", action="store_true", help="skip the drop-in CLI end-to-end leg")
     ap.add_argument("--flags", type=int, default=0, help="sab_config.flags (tuning / A-B runs)")

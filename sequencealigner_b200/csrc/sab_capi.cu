@@ -141,7 +141,10 @@ int ensure(sab_ctx *ctx, void **p, size_t *cap, size_t need, size_t elem)
 }
 
 // Kernel variants: [narrow] strip width 32 (4 resident blocks/SM) or 16 (5 blocks/SM).
-constexpr int kStripWide = 32, kStripNarrow = 16;
+#ifndef SAB_STRIP_WIDE
+#define SAB_STRIP_WIDE 32
+#endif
+constexpr int kStripWide = SAB_STRIP_WIDE, kStripNarrow = 16;
 #ifndef SAB_MINB_WIDE
 #define SAB_MINB_WIDE 4
 #endif

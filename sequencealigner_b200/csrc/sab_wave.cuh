@@ -154,7 +154,11 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 
 	CellK<METHOD, PACKED> ck;
 	ck.one = p.one;
+#ifdef SAB_IMM_LG // experiment (valid for -s 10 -e 1 only): the lane constant as an immediate operand
+	ck.lG = PACKED ? (METHOD == M_GA ? 0xfff7fff7u : 0xffffffffu) : O::lane(METHOD == M_GA ? gA - gE : gE);
+#else
 	ck.lG = O::lane(METHOD == M_GA ? gA - gE : gE);
+#endif
 	ck.dE = O::delta(gE);
 	ck.dA = O::delta(gA);
 	ck.ZERO = O::bcast(0);
@@ -272,6 +276,12 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 		int d_s = -1, d_c0 = 0, d_l0 = 0, d_l1 = 0, d_ps = 0;
 		bool first = false, last = false;
 		uint32_t V[K], Y[K];
+#ifdef SAB_PREFETCH_ROWS // experiment: the next row group's letters are loaded one step ahead
+		uint32_t wn[kGroupWords];
+#pragma unroll
+		for (int i = 0; i < kGroupWords; i++)
+			wn[i] = rowp[i * 32];
+#endif
 		uint32_t diag = 0, bestA = ck.ZERO, bestB = ck.ZERO;
 		const uint32_t *prof_s = sm.prof[0][warp][0];
 		const int T = R * G + (kWaveWarps - 1);
@@ -304,11 +314,25 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 						sm.sbest[d_ps][lane] = ck.ZERO;
 				}
 				const int r0 = g * kGroup;
+#ifdef SAB_PREFETCH_ROWS
+				uint32_t w[kGroupWords];
+				{
+					const int gn = g + 1 == G ? 0 : g + 1;
+#pragma unroll
+					for (int i = 0; i < kGroupWords; i++) {
+						w[i] = wn[i];
+						if (gn * kGroup < Lmax)
+							wn[i] = rowp[(gn * kGroupWords + i) * 32];
+					}
+				}
+#endif
 				if (d_s >= 0 && r0 < Lq) {
+#ifndef SAB_PREFETCH_ROWS
 					uint32_t w[kGroupWords];
 #pragma unroll
 					for (int i = 0; i < kGroupWords; i++)
 						w[i] = rowp[(g * kGroupWords + i) * 32];
+#endif
 					const uint2 *xin = &sm.xch[(tau - 1) & 1][warp ? warp - 1 : 0][0][lane];
 					uint2 *xout = &sm.xch[tau & 1][warp < kWaveWarps - 1 ? warp : 0][0][lane];
 					const bool from_g = warp == 0, to_g = warp == kWaveWarps - 1;

@@ -33,7 +33,11 @@ __global__ void __launch_bounds__(128, MINB) micro(uint32_t *out, int iters, int
 	__syncthreads();
 	CellK<METHOD, true> ck;
 	ck.one = one;
+#ifdef SAB_IMM_LG
+	ck.lG = METHOD == M_GA ? 0xfff7fff7u : 0xffffffffu;
+#else
 	ck.lG = O::lane(METHOD == M_GA ? gA - gE : gE);
+#endif
 	ck.dE = O::delta(gE);
 	ck.dA = O::delta(gA);
 	ck.ZERO = O::bcast(0);
