@@ -409,6 +409,7 @@ def run_ours(args):
         al.align(write=False, shard=my_shard, nshards=nsh)
     dev_ms, my_cells, launches = 0.0, 0, 0
     kernel_ms = 0.0
+    widths = {}
     barrier()
     with ClockSampler(local_rank) as clocks:
         t_wall0 = time.perf_counter()
@@ -421,6 +422,7 @@ def run_ours(args):
             kernel_ms += st["kernel_ms"]
             my_cells += st["cells"]
             launches += st["launches"]
+            widths = st["width_launches"]
         barrier()
         wall_ms = (time.perf_counter() - t_wall0) * 1e3
     clk = clocks.summary()
@@ -490,7 +492,7 @@ def run_ours(args):
     bits = 5 if c["alphabet"] != "ACGT" else 2
     alg_bytes = float(store.pairs()) * 4 + float(store.lengths.sum()) * bits / 8 * 2
     roofline = {
-        "bound": "int_alu", "kernel": f"sab_wave_kernel<{method},int16x2>",
+        "bound": "int_alu", "kernel": f"sab_wave_kernel<{method},int16x2,K> (one launch per strip width in use)",
         "achieved": achieved, "peak": int_peak, "unit": "T lane-instr/s",
         "frac": (achieved / int_peak) if int_peak else None,
         "peak_source": "measured on this box in this run by tools/pipe_peak.cu: VIADDMNMX/VIMNMX3.U16x2 "
@@ -544,7 +546,8 @@ def run_ours(args):
                 "pairs_per_s": (filt["pairs_after"] if filt else desc["pairs"]) / (e2e_ms * 1e-3),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "checksum": checksum, "steps_rank0": e2e_steps},
-        "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+        "gpu_launches": launches, "width_launches": {str(k): v for k, v in widths.items()},
+        "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
         "cli_end_to_end": cli,
     }
     print(json.dumps(out), flush=True)

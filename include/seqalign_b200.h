@@ -47,7 +47,7 @@
 extern "C" {
 #endif
 
-#define SAB_ABI_VERSION 1
+#define SAB_ABI_VERSION 2
 
 enum sab_status {
 	SAB_OK = 0,
@@ -117,6 +117,9 @@ typedef struct sab_stats {
 	int64_t rerun_strips; /* SW strips swept again in int32 because their re-run list ran full */
 	int64_t filter_matches; /* pairs that passed the threshold in the last sab_filter* (-1: sequential path) */
 	double filter_ms; /* wall time of the last sab_filter* / sab_multi_filter */
+	int32_t width_launches[16]; /* kernel launches per register-strip width, widest (32) first in steps of
+				     * 2 columns down to 16: a strip is launched once per width its subject
+				     * chunks prefer */
 } sab_stats;
 
 typedef struct sab_ctx sab_ctx;

@@ -50,6 +50,9 @@ def lib() -> C.CDLL:
         l.oracle_align_all.restype = C.c_int64
         l.oracle_align_all.argtypes = [C.POINTER(OracleConfig), C.c_void_p, C.c_void_p, C.c_int32,
                                        C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
+        l.oracle_pairs.restype = None
+        l.oracle_pairs.argtypes = [C.POINTER(OracleConfig), C.c_void_p, C.c_void_p, C.c_int64,
+                                   C.c_void_p, C.c_void_p, C.c_void_p]
         l.oracle_filter.restype = C.c_int32
         l.oracle_filter.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_float, C.c_void_p]
         _lib = l
@@ -95,6 +98,19 @@ def time_columns(resolved: dict, store, first_j: int, last_j: int):
 def pair(resolved: dict, seq_j: bytes, seq_i: bytes) -> int:
     cfg = make_config(resolved)
     return int(lib().oracle_pair(C.byref(cfg), seq_j, len(seq_j), seq_i, len(seq_i)))
+
+
+def pairs(resolved: dict, store, i: np.ndarray, j: np.ndarray) -> np.ndarray:
+    """Scores the listed (i<j) pairs (all host threads)."""
+    cfg = make_config(resolved)
+    seqs = np.ascontiguousarray(store.seqs)
+    meta = np.ascontiguousarray(store.meta)
+    i = np.ascontiguousarray(i, dtype=np.int32)
+    j = np.ascontiguousarray(j, dtype=np.int32)
+    out = np.zeros(i.size, dtype=np.int32)
+    lib().oracle_pairs(C.byref(cfg), seqs.ctypes.data, meta.ctypes.data, i.size, i.ctypes.data,
+                       j.ctypes.data, out.ctypes.data)
+    return out
 
 
 def filter_lost(store, threshold: float) -> np.ndarray:

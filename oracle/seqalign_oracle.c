@@ -235,3 +235,14 @@ int32_t oracle_filter(const uint8_t *seqs, const oracle_meta *meta, int32_t num,
 	}
 	return nlost;
 }
+
+/* A list of (i<j) pairs scored as align.c:55 scores them (sampled parity at sizes the whole
+ * matrix cannot be recomputed at): out[k] = score(is[k], js[k]).  OpenMP over the list. */
+void oracle_pairs(const oracle_config *cfg, const uint8_t *seqs, const oracle_meta *meta,
+		  int64_t n_pairs, const int32_t *is, const int32_t *js, int32_t *out)
+{
+#pragma omp parallel for schedule(dynamic, 64)
+	for (int64_t k = 0; k < n_pairs; k++)
+		out[k] = oracle_pair(cfg, seqs + meta[js[k]].off, meta[js[k]].len, seqs + meta[is[k]].off,
+				     meta[is[k]].len);
+}

@@ -15,10 +15,11 @@ CSRC = PKG / "csrc"
 LIB = PKG / "libseqalign_b200.so"
 PIPE_LIB = PKG / "libsab_pipepeak.so"
 SOURCES = ["sab_capi.cu", "sab_filter.cu", "sab_tables.cpp", "sab_h5.cpp"]
+WAVE_INST = "sab_wave_inst.cu"  # compiled once per register-strip width (-DSAB_K=<columns>)
 HEADERS = ["sab_kernels.cuh", "sab_wave.cuh", "sab_internal.h", "submat_tables.inc", "../../include/seqalign_b200.h"]
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
-    "-Xcompiler", "-fPIC,-O3,-Wall,-Wno-unused-function", "-shared", "-cudart", "shared",
+    "-Xcompiler", "-fPIC,-O3,-Wall,-Wno-unused-function", "-cudart", "shared",
 ]
 
 
@@ -36,15 +37,44 @@ def _stale(out: Path, deps: list[Path]) -> bool:
     return any(d.exists() and d.stat().st_mtime > t for d in deps)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> Path:
-    srcs = [CSRC / s for s in SOURCES if (CSRC / s).exists()]
-    deps = srcs + [CSRC / h for h in HEADERS]
-    if force or _stale(LIB, deps):
-        cmd = [nvcc(), *NVCC_FLAGS, "-o", str(LIB), *map(str, srcs), "-lz"]
-        if verbose:
-            cmd.insert(1, "-Xptxas=-v")
-        subprocess.run(cmd, check=True, cwd=str(CSRC))
-    return LIB
+def strip_widths() -> list[int]:
+    """The widths the kernel is instantiated for: the SAB_WIDTHS list of csrc/sab_kernels.cuh."""
+    import re
+    m = re.search(r"#define SAB_WIDTHS\(X\)(.*)", (CSRC / "sab_kernels.cuh").read_text())
+    return [int(k) for k in re.findall(r"X\((\d+)\)", m.group(1))]
+
+
+def build_library(force: bool = False, verbose: bool = False, out: Path | None = None,
+                  defines: tuple[str, ...] = ()) -> Path:
+    """nvcc -c every translation unit (in parallel: the strip kernel is ~64 KB of unrolled code per
+    instantiation, 33 of them), then link.  `out` / `defines` build tuning variants."""
+    from concurrent.futures import ThreadPoolExecutor
+    out = Path(out or LIB)
+    srcs = [CSRC / s for s in SOURCES]
+    deps = srcs + [CSRC / WAVE_INST] + [CSRC / h for h in HEADERS]
+    if not (force or _stale(out, deps)):
+        return out
+    objdir = PKG / "_obj" / out.stem
+    objdir.mkdir(parents=True, exist_ok=True)
+    base = [nvcc(), *NVCC_FLAGS, *defines] + (["-Xptxas=-v"] if verbose else [])
+    jobs = [(base + ["-c", str(src), "-o", str(objdir / (src.stem + ".o"))]) for src in srcs]
+    jobs += [(base + [f"-DSAB_K={k}", "-c", str(CSRC / WAVE_INST), "-o", str(objdir / f"sab_wave_k{k}.o")])
+             for k in strip_widths()]
+
+    def run(cmd):
+        return subprocess.run(cmd, cwd=str(CSRC), capture_output=True, text=True)
+
+    with ThreadPoolExecutor(max_workers=max(2, (os.cpu_count() or 4))) as ex:
+        results = list(ex.map(run, jobs))
+    for cmd, r in zip(jobs, results):
+        if verbose or r.returncode:
+            print(" ".join(cmd[-4:]), r.stdout, r.stderr, sep="\n")
+        if r.returncode:
+            raise subprocess.CalledProcessError(r.returncode, cmd, r.stdout, r.stderr)
+    objs = [c[-1] for c in jobs]
+    subprocess.run([nvcc(), "-shared", "-cudart", "shared", "-gencode", "arch=compute_100a,code=sm_100a",
+                    "-o", str(out), *objs, "-lz"], check=True, cwd=str(CSRC))
+    return out
 
 
 def build_pipe_peak(force: bool = False) -> Path:
@@ -53,11 +83,17 @@ def build_pipe_peak(force: bool = False) -> Path:
     tools = PKG.parent / "tools"
     srcs = [tools / "pipe_peak.cu", tools / "cell_peak.cu"]
     if force or _stale(PIPE_LIB, srcs + [CSRC / "sab_wave.cuh", CSRC / "sab_kernels.cuh"]):
-        subprocess.run([nvcc(), *NVCC_FLAGS, "-DCELL_PEAK_LIB", "-I", str(CSRC), "-I", str(PKG.parent / "include"),
+        subprocess.run([nvcc(), *NVCC_FLAGS, "-shared", "-DCELL_PEAK_LIB", "-I", str(CSRC), "-I", str(PKG.parent / "include"),
                         "-o", str(PIPE_LIB), *map(str, srcs)], check=True)
     return PIPE_LIB
 
 
 if __name__ == "__main__":
-    print(build_library(force=True, verbose=True))
-    print(build_pipe_peak(force=True))
+    import sys
+    if len(sys.argv) > 2 and sys.argv[1] == "--variant":  # tuning builds: --variant <name> [-D...]
+        (PKG / "_variants").mkdir(exist_ok=True)
+        print(build_library(force=True, out=PKG / "_variants" / f"{sys.argv[2]}.so",
+                            defines=tuple(sys.argv[3:])))
+    else:
+        print(build_library(force=True, verbose="-v" in sys.argv))
+        print(build_pipe_peak(force=True))

@@ -47,10 +47,13 @@ class SabStats(C.Structure):
         ("launches", C.c_int64), ("tiles", C.c_int64), ("tiles_int32", C.c_int64),
         ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64), ("rerun_strips", C.c_int64),
         ("filter_matches", C.c_int64), ("filter_ms", C.c_double),
+        ("width_launches", C.c_int32 * 16),
     ]
 
     def as_dict(self):
-        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
+        d = {n: getattr(self, n) for n, _ in self._fields_ if n != "width_launches"}
+        d["width_launches"] = {32 - 2 * w: int(v) for w, v in enumerate(self.width_launches) if v}
+        return d
 
 
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_int64, C.c_int64, C.c_void_p)
@@ -118,7 +121,7 @@ def load(path: Path | None = None) -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export it
         fn.restype = res
         fn.argtypes = args
-    if lib.sab_abi_version() != 1:
+    if lib.sab_abi_version() != 2:
         raise RuntimeError("libseqalign_b200.so ABI version mismatch")
     if path is None:
         _lib = lib

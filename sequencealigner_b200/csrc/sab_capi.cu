@@ -11,8 +11,8 @@
 // There is no CPU fallback in this file: without a usable sm_100 device every
 // compute entry point returns SAB_ERR_NODEVICE / SAB_ERR_CUDA.
 #include "sab_internal.h"
+#define SAB_WITH_RERUN_KERNEL
 #include "sab_kernels.cuh"
-#include "sab_wave.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -54,6 +54,9 @@ struct StripBuf {
 	uint2 *bnd = nullptr;
 	size_t bnd_cap = 0;
 	unsigned *counter = nullptr; // [0] work counter, [1] rerun count
+	int *chunk_ids = nullptr; // per-width lists of subject chunks of the strip in flight
+	size_t chunk_ids_cap = 0;
+	std::vector<int> chunk_host;
 	unsigned long long *rerun_list = nullptr;
 	int32_t *rerun_scratch = nullptr;
 	size_t rerun_scratch_cap = 0;
@@ -90,7 +93,10 @@ struct sab_ctx {
 	cudaStream_t copy_stream = nullptr;
 	cudaEvent_t ev_copy[2] = { nullptr, nullptr };
 	cudaEvent_t ev_span[2] = { nullptr, nullptr }; // first kernel start / last kernel end
-	int wave_blocks[3][2][2]{}; // [method][packed][narrow] resident persistent blocks, 0 = not set up yet
+	struct Variant { // [method][packed][width index], set up on first use (wave_variant)
+		void (*fn)(const sab::TileParams) = nullptr;
+		int smem = 0, grid = 0;
+	} variants[3][2][16];
 	bool sw_prefer_int32 = false; // a strip's re-run list overflowed: later risky strips start in int32
 	sab_stats stats{};
 	// sab_filter.cu keeps its device buffers here (released by sab_destroy)
@@ -122,8 +128,6 @@ int fail(sab_ctx *c, int code, const char *fmt, ...)
 				    __LINE__);                                                \
 	} while (0)
 
-typedef void (*tile_kernel_t)(const TileParams);
-
 // grow-only device buffer
 int ensure(sab_ctx *ctx, void **p, size_t *cap, size_t need, size_t elem)
 {
@@ -140,59 +144,49 @@ int ensure(sab_ctx *ctx, void **p, size_t *cap, size_t need, size_t elem)
 	return SAB_OK;
 }
 
-// Kernel variants: [narrow] strip width 32 (4 resident blocks/SM) or 16 (5 blocks/SM).
-#ifndef SAB_STRIP_WIDE
-#define SAB_STRIP_WIDE 32
-#endif
-constexpr int kStripWide = SAB_STRIP_WIDE, kStripNarrow = 16;
-#ifndef SAB_MINB_WIDE
-#define SAB_MINB_WIDE 4
-#endif
-#ifndef SAB_MINB_NARROW
-#define SAB_MINB_NARROW 5
-#endif
-constexpr int kMinbWide = SAB_MINB_WIDE, kMinbNarrow = SAB_MINB_NARROW;
+// Register-strip widths (DP columns a warp holds in registers).  The kernel is instantiated once
+// per width (sab_wave_inst.cu); a row strip is launched once per width that some of its subject
+// chunks prefer (choose_widths), so subjects pad to the next multiple of THEIR best width instead
+// of a global 32 or 16.  Widest first; int32 strips use the first and the last entry only.
+struct WidthInfo {
+	int k;
+	sab::wave_kernel_t (*get)(int method, bool packed, int *smem_bytes, int *minb);
+};
+#define SAB_WIDTH_ENTRY(K) { K, sab::wave_kernel_k##K },
+constexpr WidthInfo kWidths[] = { SAB_WIDTHS(SAB_WIDTH_ENTRY) };
+#undef SAB_WIDTH_ENTRY
+constexpr int kNumWidths = (int)(sizeof(kWidths) / sizeof(kWidths[0]));
+constexpr int kWidest = 0, kNarrowest = kNumWidths - 1;
+static_assert(kNumWidths <= 16 && kWidths[kWidest].k == sab::kStrip, "width table");
 
-template <int K, int MINB> tile_kernel_t pick_wave_kernel_t(int method, bool packed)
+// Relative cost of one DP column in a strip of width K: a step carries the same bookkeeping
+// (~165 instructions) whatever its width.  Calibrated on B200: a 16-column step costs 5.5 % more
+// per column than a 32-column one (profiles/r1_cell_shape_ceiling.md) -> 1 + 1.87 / K.
+inline double column_cost(int k)
 {
-	switch (method * 2 + (packed ? 1 : 0)) {
-	case 0: return sab::sab_wave_kernel<sab::M_NW, false, K, MINB>;
-	case 1: return sab::sab_wave_kernel<sab::M_NW, true, K, MINB>;
-	case 2: return sab::sab_wave_kernel<sab::M_GA, false, K, MINB>;
-	case 3: return sab::sab_wave_kernel<sab::M_GA, true, K, MINB>;
-	case 4: return sab::sab_wave_kernel<sab::M_SW, false, K, MINB>;
-	default: return sab::sab_wave_kernel<sab::M_SW, true, K, MINB>;
-	}
+	return 1.0 + 1.87 / k;
 }
 
-tile_kernel_t pick_wave_kernel(int method, bool packed, bool narrow)
-{
-	return narrow ? pick_wave_kernel_t<kStripNarrow, kMinbNarrow>(method, packed) :
-			pick_wave_kernel_t<kStripWide, kMinbWide>(method, packed);
-}
+typedef sab_ctx::Variant WaveVariant;
 
-int wave_smem_bytes(bool narrow)
+// One kernel variant, set up on first use (dynamic shared memory attribute + occupancy query:
+// ~1 ms each; a job launches a handful of the 33).
+int wave_variant(sab_ctx *ctx, int method, bool packed, int widx, WaveVariant *out)
 {
-	return narrow ? (int)sizeof(sab::WaveSmem<kStripNarrow>) : (int)sizeof(sab::WaveSmem<kStripWide>);
-}
-
-// Resident persistent blocks of one kernel variant; sets the variant up on first use
-// (dynamic shared memory attribute + occupancy query: ~1 ms each, a job needs one or two).
-int wave_variant(sab_ctx *ctx, int method, bool packed, bool narrow, int *grid)
-{
-	int &slot = ctx->wave_blocks[method][packed][narrow];
-	if (!slot) {
-		int occ = 0;
-		tile_kernel_t wk = pick_wave_kernel(method, packed, narrow);
-		CU(cudaFuncSetAttribute((const void *)wk, cudaFuncAttributeMaxDynamicSharedMemorySize,
-					wave_smem_bytes(narrow)));
-		CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)wk, sab::kWaveThreads,
-								 wave_smem_bytes(narrow)));
+	WaveVariant &v = ctx->variants[method][packed][widx];
+	if (!v.fn) {
+		int minb = 0, occ = 0;
+		sab::wave_kernel_t fn = kWidths[widx].get(method, packed, &v.smem, &minb);
+		if (!fn)
+			return fail(ctx, SAB_ERR_STATE, "no int32 kernel of width %d", kWidths[widx].k);
+		CU(cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, v.smem));
+		CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)fn, sab::kWaveThreads, v.smem));
 		if (occ < 1)
 			return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
-		slot = occ * ctx->sm_count;
+		v.grid = occ * ctx->sm_count;
+		v.fn = fn;
 	}
-	*grid = slot;
+	*out = v;
 	return SAB_OK;
 }
 
@@ -220,6 +214,9 @@ void free_bufs(sab_ctx *c)
 		cudaFree(b.blkT);
 		cudaFree(b.bnd);
 		cudaFree(b.rerun_scratch);
+		cudaFree(b.chunk_ids);
+		b.chunk_ids = nullptr;
+		b.chunk_ids_cap = 0;
 		b.blk = b.blkT = nullptr;
 		b.bnd = nullptr;
 		b.rerun_scratch = nullptr;
@@ -740,7 +737,8 @@ struct Strip {
 	int a0, an; // original index range == slot range
 	double cost; // sum len_q * sum len_s (approx. cells)
 	bool packed;
-	bool narrow; // 16-column register strips (short subjects)
+	int widx_fixed; // index into kWidths when the whole strip runs at one width (int32 strips, the
+			// STRIP32/STRIP16 flags), -1 = per subject chunk (choose_widths)
 	int lq, ls; // longest query / subject
 	double mean_ls; // mean subject length (strip width and chunk size heuristics)
 };
@@ -768,16 +766,22 @@ void plan_strips(const sab_ctx *ctx, int nshards, std::vector<Strip> &strips, st
 		const double ls_sum = (double)ctx->len_prefix[s.a0] + 0.5 * lq_sum;
 		s.cost = lq_sum * ls_sum;
 		s.packed = !force32 && (force16 || int16_safe(ctx, s.lq, s.ls));
-		// Strip width: the subjects of this strip (every slot below its last query) padded to 16
-		// or to 32 DP columns.  A 16-column step carries the same bookkeeping as a 32-column one
-		// for half the cells: measured 5.5 % more time per padded column (C3, len 150: 6.11 vs
-		// 6.44 TCUPS at equal padding), so the narrow kernel must save more than that.
+		// Strip width: packed strips choose it per subject chunk at launch time (choose_widths).
+		// int32 strips exist at the widest and the narrowest width only: the subjects of the strip
+		// (every slot below its last query) padded to 16 or to 32 DP columns, weighted by what a
+		// column costs at either width.
 		const int a1 = s.a0 + s.an;
 		const double mean_ls = (double)ctx->len_prefix[a1] / a1;
 		s.mean_ls = mean_ls;
 		const double cols16 = (double)ctx->pad16_prefix[a1], cols32 = (double)ctx->pad32_prefix[a1];
-		s.narrow = (ctx->cfg.flags & SAB_FLAG_STRIP16) ||
-			   (!(ctx->cfg.flags & SAB_FLAG_STRIP32) && cols16 * 1.055 < cols32);
+		if (ctx->cfg.flags & SAB_FLAG_STRIP16)
+			s.widx_fixed = kNarrowest;
+		else if (ctx->cfg.flags & SAB_FLAG_STRIP32)
+			s.widx_fixed = kWidest;
+		else if (!s.packed)
+			s.widx_fixed = cols16 * column_cost(16) < cols32 * column_cost(32) ? kNarrowest : kWidest;
+		else
+			s.widx_fixed = -1;
 	}
 	std::vector<double> cost(npanels);
 	for (int p = 0; p < npanels; p++)
@@ -908,6 +912,65 @@ void issue_order(const sab_ctx *ctx, const std::vector<Strip> &strips, std::vect
 			 [&](int x, int y) { return strips[x].cost > strips[y].cost; });
 }
 
+// Register-strip width per subject chunk of a packed strip.  Slots are length-sorted inside a
+// panel, so the 16..128 subjects of a chunk have near-equal lengths and one width fits them all:
+// the one that minimises sum(ceil(pair length / K) * K) * column_cost(K).  Widths that only a
+// few chunks ask for are folded into the others (a launch per width has a start and a tail).
+// Out: ids = chunk indices grouped by width, first[w]..first[w+1] the group of kWidths[w].
+void choose_widths(const sab_ctx *ctx, int a1, int chunk, int nsc, std::vector<int> &ids, int *first)
+{
+	std::vector<uint8_t> best((size_t)nsc);
+	std::vector<float> cost((size_t)nsc * kNumWidths);
+	int count[kNumWidths] = { 0 };
+	bool enabled[kNumWidths];
+	for (int w = 0; w < kNumWidths; w++)
+		enabled[w] = true;
+	const int32_t *len = ctx->slot_len.data();
+	for (int k = 0; k < nsc; k++) {
+		const int s0 = k * chunk, s1 = std::min(a1, s0 + chunk);
+		double c[kNumWidths] = { 0 };
+		for (int s = s0; s < s1; s += 2) {
+			const int l = s + 1 < s1 ? std::max(len[s], len[s + 1]) : len[s];
+			for (int w = 0; w < kNumWidths; w++) {
+				const int kk = kWidths[w].k;
+				c[w] += (double)((l + kk - 1) / kk * kk);
+			}
+		}
+		for (int w = 0; w < kNumWidths; w++)
+			cost[(size_t)k * kNumWidths + w] = (float)(c[w] * column_cost(kWidths[w].k));
+	}
+	for (int pass = 0; pass < 2; pass++) {
+		for (int w = 0; w < kNumWidths; w++)
+			count[w] = 0;
+		for (int k = 0; k < nsc; k++) {
+			int bw = -1;
+			for (int w = 0; w < kNumWidths; w++)
+				if (enabled[w] && (bw < 0 || cost[(size_t)k * kNumWidths + w] < cost[(size_t)k * kNumWidths + bw]))
+					bw = w;
+			best[k] = (uint8_t)bw;
+			count[bw]++;
+		}
+		if (pass == 0) {
+			const int floor_ = std::max(4, nsc / 50);
+			int top = 0;
+			for (int w = 1; w < kNumWidths; w++)
+				if (count[w] > count[top])
+					top = w;
+			for (int w = 0; w < kNumWidths; w++)
+				enabled[w] = w == top || count[w] >= floor_;
+		}
+	}
+	first[0] = 0;
+	for (int w = 0; w < kNumWidths; w++)
+		first[w + 1] = first[w] + count[w];
+	ids.resize((size_t)nsc);
+	int fill[kNumWidths];
+	for (int w = 0; w < kNumWidths; w++)
+		fill[w] = first[w];
+	for (int k = 0; k < nsc; k++)
+		ids[fill[best[k]]++] = k;
+}
+
 int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &src, int64_t pairs_total,
 		 int32_t *matrix, int triangular, sab_progress_fn progress, void *user)
 {
@@ -936,14 +999,9 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 
 	auto launch = [&](const Strip &st, StripBuf &b) -> int {
 		const bool packed = st.packed;
-		const bool narrow = st.narrow;
-		int grid = 0;
-		int rc = wave_variant(ctx, method, packed, narrow, &grid);
-		if (rc)
-			return rc;
 		const int a1 = st.a0 + st.an;
 		const size_t blk_elems = (size_t)(tri(a1) - tri(st.a0));
-		rc = ensure(ctx, (void **)&b.blk, &b.blk_cap, std::max<size_t>(blk_elems, 1), sizeof(int32_t));
+		int rc = ensure(ctx, (void **)&b.blk, &b.blk_cap, std::max<size_t>(blk_elems, 1), sizeof(int32_t));
 		if (rc)
 			return rc;
 		if (!triangular && matrix) {
@@ -951,12 +1009,40 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 			if (rc)
 				return rc;
 		}
-		const size_t bnd_block = (size_t)bnd_rows * 32;
-		rc = ensure(ctx, (void **)&b.bnd, &b.bnd_cap, bnd_block * grid, sizeof(uint2));
-		if (rc)
-			return rc;
 		if (method == SAB_SW && packed && !b.rerun_list)
 			CU(cudaMalloc(&b.rerun_list, sizeof(unsigned long long) * kRerunCap));
+		// Work item = 32 queries x `chunk` subjects.  An item pays 3 steps of pipeline fill, so
+		// short subjects get more of them per item: aim at >= 24 rounds (4 strips each).
+		const int est_strips = std::max(1, (int)((st.mean_ls + sab::kStrip - 1) / sab::kStrip));
+		const int mult = std::min(8, std::max(1, (24 + 2 * est_strips - 1) / (2 * est_strips)));
+		const int chunk = (packed ? 16 : 8) * mult;
+		const int nsc = (a1 + chunk - 1) / chunk;
+		// which chunks run at which width: lists[w] = [first[w], first[w + 1]) of b.chunk_host
+		int first[kNumWidths + 1] = { 0 };
+		if (st.widx_fixed >= 0) {
+			for (int w = 0; w <= kNumWidths; w++)
+				first[w] = w > st.widx_fixed ? nsc : 0;
+		} else {
+			choose_widths(ctx, a1, chunk, nsc, b.chunk_host, first);
+			rc = ensure(ctx, (void **)&b.chunk_ids, &b.chunk_ids_cap, (size_t)nsc, sizeof(int));
+			if (rc)
+				return rc;
+			CU(cudaMemcpyAsync(b.chunk_ids, b.chunk_host.data(), sizeof(int) * nsc, cudaMemcpyHostToDevice,
+					   b.stream));
+		}
+		WaveVariant var[kNumWidths];
+		int max_grid = 0;
+		for (int w = 0; w < kNumWidths; w++)
+			if (first[w + 1] > first[w]) {
+				rc = wave_variant(ctx, method, packed, w, &var[w]);
+				if (rc)
+					return rc;
+				max_grid = std::max(max_grid, var[w].grid);
+			}
+		const size_t bnd_block = (size_t)bnd_rows * 32;
+		rc = ensure(ctx, (void **)&b.bnd, &b.bnd_cap, bnd_block * max_grid, sizeof(uint2));
+		if (rc)
+			return rc;
 		TileParams p{};
 		p.seqs = dseqs;
 		p.a_slot0 = st.a0;
@@ -965,15 +1051,7 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 		p.blk = b.blk;
 		p.tri0 = tri(st.a0);
 		p.blkT = (!triangular && matrix) ? b.blkT : nullptr;
-		// Work item = 32 queries x `chunk` subjects.  An item pays 3 steps of pipeline fill, so
-		// short subjects get more of them per item: aim at >= 24 rounds (4 strips each).
-		{
-			const int width = narrow ? kStripNarrow : kStripWide;
-			const int nstrips = std::max(1, (int)((st.mean_ls + width - 1) / width));
-			const int mult = std::min(8, std::max(1, (24 + 2 * nstrips - 1) / (2 * nstrips)));
-			p.chunk = (packed ? 16 : 8) * mult;
-		}
-		p.nsc = (a1 + p.chunk - 1) / p.chunk;
+		p.chunk = chunk;
 		p.counter = b.counter;
 		p.bnd = b.bnd;
 		p.bnd_block_stride = (int64_t)bnd_block;
@@ -991,11 +1069,21 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 		if (S.launches == 0)
 			CU(cudaEventRecord(ctx->ev_span[0], b.stream));
 		CU(cudaEventRecord(b.ev_start, b.stream));
-		pick_wave_kernel(method, packed, narrow)
-			<<<grid, sab::kWaveThreads, wave_smem_bytes(narrow), b.stream>>>(p);
-		CU(cudaGetLastError());
+		bool first_launch = true;
+		for (int w = 0; w < kNumWidths; w++) { // one launch per width in use, back to back
+			p.nsc = first[w + 1] - first[w];
+			if (p.nsc <= 0)
+				continue;
+			p.chunk_ids = st.widx_fixed >= 0 ? nullptr : b.chunk_ids + first[w];
+			if (!first_launch) // the work counter restarts, the re-run count accumulates
+				CU(cudaMemsetAsync(b.counter, 0, sizeof(unsigned), b.stream));
+			first_launch = false;
+			var[w].fn<<<var[w].grid, sab::kWaveThreads, var[w].smem, b.stream>>>(p);
+			CU(cudaGetLastError());
+			S.launches++;
+			S.width_launches[w]++;
+		}
 		CU(cudaEventRecord(b.ev_done, b.stream));
-		S.launches++;
 		S.tiles++;
 		if (!packed)
 			S.tiles_int32++;
@@ -1472,6 +1560,8 @@ int sab_multi_align(sab_multi *m, int32_t *matrix, int triangular, sab_progress_
 		S.cells += s.cells;
 		S.rerun_pairs += s.rerun_pairs;
 		S.rerun_strips += s.rerun_strips;
+		for (int w = 0; w < 16; w++)
+			S.width_launches[w] += s.width_launches[w];
 		S.launches += s.launches;
 		S.tiles += s.tiles;
 		S.tiles_int32 += s.tiles_int32;

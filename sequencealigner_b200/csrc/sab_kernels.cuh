@@ -36,6 +36,15 @@ constexpr int kProfStride = 25; // words per profile column (coprime with 32 ban
 
 enum { M_NW = 0, M_GA = 1, M_SW = 2 };
 
+constexpr int kWaveWarps = 4; // warps of a block = consecutive strips of the strip pipeline (sab_wave.cuh)
+constexpr int kWaveThreads = kWaveWarps * 32;
+
+// what the profile entries are shifted by (host: sub25 = S - shift; device: the skewed cell of sab_wave.cuh)
+__host__ __device__ inline int profile_shift(int method, int gapA, int gapE)
+{
+	return method == M_NW ? 2 * gapA : method == M_GA ? 2 * gapE : gapA;
+}
+
 // Device-resident sequence store (built by sab_upload).
 struct DeviceSeqs {
 	const int32_t *slot_len; // [nslots]   length of the sequence in slot s
@@ -59,6 +68,9 @@ struct TileParams {
 	int64_t tri0; // tri(a_orig0)
 	int32_t *blkT; // optional mirror for the full layout: blkT[lo * a_n + (hi - a_orig0)]
 	int nsc, chunk; // work items = query groups of 32 x nsc subject chunks of `chunk` slots
+	const int *chunk_ids; // the nsc chunks this launch covers (nullptr: chunks 0..nsc-1); a strip is
+			      // launched once per register-strip width, each launch taking the chunks
+			      // whose subjects pad least at that width
 	unsigned *counter; // dynamic work counter of this launch
 	uint2 *bnd; // wrap-around boundary rows, one buffer per block
 	int64_t bnd_block_stride; // uint2 elements per block
@@ -71,6 +83,15 @@ struct TileParams {
 	unsigned *rerun_count;
 	unsigned rerun_cap;
 };
+
+typedef void (*wave_kernel_t)(const TileParams);
+
+// Register-strip widths the strip kernel is built for (sab_wave_inst.cu, one translation unit
+// per width) and the getters those units export.
+#define SAB_WIDTHS(X) X(32) X(30) X(28) X(26) X(24) X(22) X(20) X(18) X(16)
+#define SAB_DECLARE_WIDTH(K) wave_kernel_t wave_kernel_k##K(int method, bool packed, int *smem_bytes, int *minb);
+SAB_WIDTHS(SAB_DECLARE_WIDTH)
+#undef SAB_DECLARE_WIDTH
 
 // ---------------------------------------------------------------------------------------
 // Vector ops: two int16 lanes per register (Blackwell DPX) or one int32.
@@ -167,6 +188,7 @@ struct RerunParams {
 	int32_t *blkT;
 };
 
+#ifdef SAB_WITH_RERUN_KERNEL // defined by the one translation unit that launches it (sab_capi.cu)
 __global__ void sab_rerun_sw_kernel(const RerunParams p)
 {
 	const unsigned n = min(*p.count, p.cap);
@@ -212,5 +234,6 @@ __global__ void sab_rerun_sw_kernel(const RerunParams p)
 			p.blkT[(int64_t)lo * p.a_n + (hi - p.a_orig0)] = best;
 	}
 }
+#endif // SAB_WITH_RERUN_KERNEL
 
 } // namespace sab

@@ -44,8 +44,6 @@
 
 namespace sab {
 
-constexpr int kWaveWarps = 4;
-constexpr int kWaveThreads = kWaveWarps * 32;
 #ifndef SAB_KGROUP
 #define SAB_KGROUP 8
 #endif
@@ -66,12 +64,6 @@ template <int K> struct WaveSmem {
 	int desc[2][kWaveWarps][8]; // strip descriptors, parity = round & 1
 	int item;
 };
-
-// what the profile entries are shifted by (host: sub25 = S - shift)
-__host__ __device__ inline int profile_shift(int method, int gapA, int gapE)
-{
-	return method == M_NW ? 2 * gapA : method == M_GA ? 2 * gapE : gapA;
-}
 
 // Per-launch constants of the cell update, in the lane format of VOps<PACKED>.
 template <int METHOD, bool PACKED> struct CellK {
@@ -184,7 +176,8 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 			break;
 		// longest first: slots are sorted by ascending length inside a panel
 		const int qg = nqg - 1 - item / p.nsc;
-		const int sc = p.nsc - 1 - item % p.nsc;
+		const int ck_i = p.nsc - 1 - item % p.nsc;
+		const int sc = p.chunk_ids ? p.chunk_ids[ck_i] : ck_i;
 		const int t0 = p.a_slot0 + qg * 32;
 		const int t = t0 + lane; // my query slot
 		const bool valid = t < a_end;

@@ -20,13 +20,13 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), name
     assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
-    assert capi.load().sab_abi_version() == 1
+    assert capi.load().sab_abi_version() == 2
 
 
 def test_struct_sizes_match_header():
     assert C.sizeof(capi.SabMeta) == 8
     assert C.sizeof(capi.SabConfig) == 4 * (4 + 128 + 576 + 4 + 4)
-    assert C.sizeof(capi.SabStats) == 8 * 16
+    assert C.sizeof(capi.SabStats) == 8 * 16 + 4 * 16
 
 
 def test_no_cpu_fallback_without_device():

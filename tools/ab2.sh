@@ -3,9 +3,5 @@
 V="$1"; shift
 for v in $V; do
   if [ "$v" = default ]; then unset SAB_LIB; else export SAB_LIB=$PWD/sequencealigner_b200/_variants/$v.so; fi
-  timeout 600 python bench.py --no-cpu --no-cli --steps 2 --warmup 1 "$@" 2>/dev/null | python -c "
-import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1])
-r=d['roofline']
-print('lib=$v', '$*', '|', d['config']['workload'][:48], 'value=%.0f e2e=%.0f frac=%.3f' % (d['value'], d['e2e']['value'], r['frac'] or 0))"
+  timeout 600 python bench.py --no-cpu --no-cli --steps 2 --warmup 1 "$@" 2>/dev/null | python tools/ab_line.py "lib=$v" "$@"
 done
