@@ -34,7 +34,7 @@ using sab::TileParams;
 constexpr int kPanelQuantum = 128; // panels are multiples of 4 query groups
 constexpr size_t kStageBytes = 32u << 20; // pinned bounce buffer (x2)
 constexpr unsigned kRerunCap = 1u << 20;
-constexpr int kRerunThreads = 4096;
+constexpr int kRerunBlock = 128;
 
 double now_ms()
 {
@@ -584,18 +584,26 @@ void sab_destroy(sab_ctx *ctx)
 	delete ctx;
 }
 
-int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t num, int32_t max)
+} // extern "C"
+
+namespace {
+
+// The sequence set in its two device layouts, packed once on the host;
+// sab_multi_upload hands the same object to every device.
+struct PackedSet {
+	int32_t num = 0, max_len = 0, panel = 0;
+	std::vector<int32_t> slot_len, slot_orig, panel_maxlen;
+	std::vector<int64_t> col_off, grp_off, len_prefix, pad16_prefix, pad32_prefix;
+	std::vector<uint8_t> col_bytes;
+	std::vector<uint32_t> rowpack;
+};
+
+// Argument checks + length binning + packing.  `ctx` supplies the configuration (LUT, panel,
+// shards hint, ranges) and receives the error text.
+int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t num, int32_t max, PackedSet &ps)
 {
-	if (!ctx)
-		return SAB_ERR_ARG;
-	if (!ctx->sm_count)
-		return fail(ctx, SAB_ERR_STATE, "context has no device");
 	if (!seqs || !meta || num < 2)
 		return fail(ctx, SAB_ERR_ARG, "need at least 2 sequences (SEQ_N_MIN, align.h:21)");
-	const double t0 = now_ms();
-	CU(cudaSetDevice(ctx->cfg.device));
-	ctx->uploaded = false; // device buffers are kept and reused when large enough
-
 	int32_t real_max = 0;
 	int64_t letters = 0;
 	for (int32_t k = 0; k < num; k++) {
@@ -616,33 +624,40 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 	const int npanels = (num + panel - 1) / panel;
 
 	// Length binning: stable sort by length inside each panel -> slots.
-	std::vector<int32_t> slot_orig(num), slot_len(num);
+	std::vector<int32_t> &slot_orig = ps.slot_orig, &slot_len = ps.slot_len;
+	slot_orig.resize(num);
+	slot_len.resize(num);
 	std::iota(slot_orig.begin(), slot_orig.end(), 0);
-	std::vector<int32_t> panel_maxlen(npanels, 0);
+	ps.panel_maxlen.assign(npanels, 0);
 	for (int p = 0; p < npanels; p++) {
 		auto b = slot_orig.begin() + (size_t)p * panel;
 		auto e = slot_orig.begin() + std::min<size_t>((size_t)(p + 1) * panel, num);
 		std::stable_sort(b, e, [&](int32_t x, int32_t y) { return meta[x].len < meta[y].len; });
-		panel_maxlen[p] = meta[*(e - 1)].len;
+		ps.panel_maxlen[p] = meta[*(e - 1)].len;
 	}
-	std::vector<int64_t> col_off(num), len_prefix(num + 1), pad16_prefix(num + 1), pad32_prefix(num + 1);
+	std::vector<int64_t> &col_off = ps.col_off;
+	col_off.resize(num);
+	ps.len_prefix.resize(num + 1);
+	ps.pad16_prefix.resize(num + 1);
+	ps.pad32_prefix.resize(num + 1);
 	int64_t off = 0, off16 = 0, off32 = 0;
 	for (int32_t s = 0; s < num; s++) {
 		slot_len[s] = meta[slot_orig[s]].len;
 		col_off[s] = off;
-		len_prefix[s] = off;
-		pad16_prefix[s] = off16;
-		pad32_prefix[s] = off32;
+		ps.len_prefix[s] = off;
+		ps.pad16_prefix[s] = off16;
+		ps.pad32_prefix[s] = off32;
 		off += slot_len[s];
 		off16 += (slot_len[s] + 15) / 16 * 16;
 		off32 += (slot_len[s] + 31) / 32 * 32;
 	}
-	len_prefix[num] = off;
-	pad16_prefix[num] = off16;
-	pad32_prefix[num] = off32;
+	ps.len_prefix[num] = off;
+	ps.pad16_prefix[num] = off16;
+	ps.pad32_prefix[num] = off32;
 
 	// Subject layout: one byte per residue, index 0..23.
-	std::vector<uint8_t> col_bytes((size_t)letters + 16, 24);
+	std::vector<uint8_t> &col_bytes = ps.col_bytes;
+	col_bytes.assign((size_t)letters + 16, 24);
 	std::atomic<int32_t> bad_seq{ -1 };
 	parallel_ranges(num, letters, [&](int32_t s0, int32_t s1) {
 		for (int32_t s = s0; s < s1; s++) {
@@ -665,7 +680,8 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 	// Query layout: 32-slot groups, 4 residues per word (stored as byte offsets
 	// letter*4 into a profile column), lane-interleaved for coalesced loads.
 	const int ngroups = (num + 31) / 32;
-	std::vector<int64_t> grp_off(ngroups);
+	std::vector<int64_t> &grp_off = ps.grp_off;
+	grp_off.resize(ngroups);
 	int64_t rows4 = 0;
 	for (int g = 0; g < ngroups; g++) {
 		grp_off[g] = rows4;
@@ -676,7 +692,8 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 		rows4 += (gmax + 3) / 4 + 2; // + prefetch slack
 	}
 	// rows past a sequence's end hold the pad letter (24): SW sweeps them (sab_wave.cuh)
-	std::vector<uint32_t> rowpack((size_t)rows4 * 32, 0x60606060u);
+	std::vector<uint32_t> &rowpack = ps.rowpack;
+	rowpack.assign((size_t)rows4 * 32, 0x60606060u);
 	parallel_ranges(num, letters, [&](int32_t s0, int32_t s1) { // every slot owns its own words
 		for (int32_t s = s0; s < s1; s++) {
 			const uint8_t *src = col_bytes.data() + col_off[s];
@@ -688,43 +705,84 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 			}
 		}
 	});
+	ps.num = num;
+	ps.max_len = real_max;
+	ps.panel = panel;
+	return SAB_OK;
+}
 
+// Copies a packed set to the context's device; `keep` = the host tables may be moved out of `ps`.
+int install_set(sab_ctx *ctx, PackedSet &ps, bool keep)
+{
+	if (!ctx->sm_count)
+		return fail(ctx, SAB_ERR_STATE, "context has no device");
+	CU(cudaSetDevice(ctx->cfg.device));
+	ctx->uploaded = false; // device buffers are kept and reused when large enough
+	const int32_t num = ps.num;
+	const int ngroups = (int)ps.grp_off.size();
 	// cudaFree / cudaMalloc per upload cost 0.1-0.25 s every few calls (measured): grow-only reuse
 	{
 		void **ptr[6] = { (void **)&ctx->d_slot_len, (void **)&ctx->d_slot_orig, (void **)&ctx->d_col_off,
 				  (void **)&ctx->d_grp_off, (void **)&ctx->d_col_bytes, (void **)&ctx->d_rowpack };
 		const size_t need[6] = { sizeof(int32_t) * num, sizeof(int32_t) * num, sizeof(int64_t) * num,
-					 sizeof(int64_t) * ngroups, col_bytes.size(),
-					 rowpack.size() * sizeof(uint32_t) };
+					 sizeof(int64_t) * ngroups, ps.col_bytes.size(),
+					 ps.rowpack.size() * sizeof(uint32_t) };
 		for (int i = 0; i < 6; i++) {
 			const int rc = ensure(ctx, ptr[i], &ctx->cap_seqs[i], need[i], 1);
 			if (rc)
 				return rc;
 		}
 	}
-	CU(cudaMemcpy(ctx->d_slot_len, slot_len.data(), sizeof(int32_t) * num, cudaMemcpyHostToDevice));
-	CU(cudaMemcpy(ctx->d_slot_orig, slot_orig.data(), sizeof(int32_t) * num,
+	CU(cudaMemcpy(ctx->d_slot_len, ps.slot_len.data(), sizeof(int32_t) * num, cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_slot_orig, ps.slot_orig.data(), sizeof(int32_t) * num, cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_col_off, ps.col_off.data(), sizeof(int64_t) * num, cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_grp_off, ps.grp_off.data(), sizeof(int64_t) * ngroups, cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_col_bytes, ps.col_bytes.data(), ps.col_bytes.size(), cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_rowpack, ps.rowpack.data(), ps.rowpack.size() * sizeof(uint32_t),
 		      cudaMemcpyHostToDevice));
-	CU(cudaMemcpy(ctx->d_col_off, col_off.data(), sizeof(int64_t) * num, cudaMemcpyHostToDevice));
-	CU(cudaMemcpy(ctx->d_grp_off, grp_off.data(), sizeof(int64_t) * ngroups,
-		      cudaMemcpyHostToDevice));
-	CU(cudaMemcpy(ctx->d_col_bytes, col_bytes.data(), col_bytes.size(), cudaMemcpyHostToDevice));
-	CU(cudaMemcpy(ctx->d_rowpack, rowpack.data(), rowpack.size() * sizeof(uint32_t),
-		      cudaMemcpyHostToDevice));
-
-	ctx->num = num;
-	ctx->max_len = real_max;
-	ctx->panel = panel;
-	ctx->slot_len.swap(slot_len);
-	ctx->slot_orig.swap(slot_orig);
-	ctx->len_prefix.swap(len_prefix);
-	ctx->pad16_prefix.swap(pad16_prefix);
-	ctx->pad32_prefix.swap(pad32_prefix);
-	ctx->panel_maxlen.swap(panel_maxlen);
-	ctx->uploaded = true;
-	ctx->stats.upload_ms = now_ms() - t0;
 	ctx->stats.h2d_bytes = (int64_t)(sizeof(int32_t) * 2 * num + sizeof(int64_t) * (num + ngroups) +
-					 col_bytes.size() + rowpack.size() * sizeof(uint32_t));
+					 ps.col_bytes.size() + ps.rowpack.size() * sizeof(uint32_t));
+	ctx->num = num;
+	ctx->max_len = ps.max_len;
+	ctx->panel = ps.panel;
+	if (keep) {
+		ctx->slot_len = ps.slot_len;
+		ctx->slot_orig = ps.slot_orig;
+		ctx->len_prefix = ps.len_prefix;
+		ctx->pad16_prefix = ps.pad16_prefix;
+		ctx->pad32_prefix = ps.pad32_prefix;
+		ctx->panel_maxlen = ps.panel_maxlen;
+	} else {
+		ctx->slot_len.swap(ps.slot_len);
+		ctx->slot_orig.swap(ps.slot_orig);
+		ctx->len_prefix.swap(ps.len_prefix);
+		ctx->pad16_prefix.swap(ps.pad16_prefix);
+		ctx->pad32_prefix.swap(ps.pad32_prefix);
+		ctx->panel_maxlen.swap(ps.panel_maxlen);
+	}
+	ctx->sw_prefer_int32 = false;
+	ctx->uploaded = true;
+	return SAB_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t num, int32_t max)
+{
+	if (!ctx)
+		return SAB_ERR_ARG;
+	if (!ctx->sm_count)
+		return fail(ctx, SAB_ERR_STATE, "context has no device");
+	const double t0 = now_ms();
+	PackedSet ps;
+	int rc = pack_set(ctx, seqs, meta, num, max, ps);
+	if (rc == SAB_OK)
+		rc = install_set(ctx, ps, false);
+	if (rc)
+		return rc;
+	ctx->stats.upload_ms = now_ms() - t0;
 	return SAB_OK;
 }
 
@@ -1117,6 +1175,12 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 				S.rerun_strips++;
 			} else if (cnt) {
 				const int cols = ctx->max_len + 1;
+				// one thread per listed pair, at most one block per SM and 512 MB of row scratch
+				const size_t per_thread = (size_t)2 * cols * sizeof(int32_t);
+				int blocks = (int)std::min<size_t>(((size_t)cnt + kRerunBlock - 1) / kRerunBlock,
+								   (size_t)ctx->sm_count);
+				blocks = (int)std::max<size_t>(1, std::min<size_t>(blocks, (512u << 20) / (per_thread * kRerunBlock)));
+				const int kRerunThreads = blocks * kRerunBlock;
 				int rc = ensure(ctx, (void **)&b.rerun_scratch, &b.rerun_scratch_cap,
 						(size_t)kRerunThreads * 2 * cols, sizeof(int32_t));
 				if (rc)
@@ -1136,7 +1200,7 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 				rp.blk = b.blk;
 				rp.tri0 = tri(st.a0);
 				rp.blkT = (!triangular && matrix) ? b.blkT : nullptr;
-				sab::sab_rerun_sw_kernel<<<kRerunThreads / 128, 128, 0, b.stream>>>(rp);
+				sab::sab_rerun_sw_kernel<<<blocks, kRerunBlock, 0, b.stream>>>(rp);
 				CU(cudaGetLastError());
 				CU(cudaEventRecord(b.ev_done, b.stream));
 				CU(cudaEventSynchronize(b.ev_done));
@@ -1507,10 +1571,20 @@ int sab_multi_upload(sab_multi *m, const uint8_t *seqs, const sab_meta *meta, in
 	if (rc)
 		return rc;
 	m->active = 0;
+	// packed once (the auto panel sized for the devices that take part in THIS job), copied to every device
+	const double t0 = now_ms();
+	m->ctx[0]->cfg.shards_hint = n;
+	PackedSet ps;
+	rc = pack_set(m->ctx[0], seqs, meta, num, max, ps);
+	if (rc) {
+		m->err = sab_last_error(m->ctx[0]);
+		return rc;
+	}
 	rc = multi_run(m, n, [&](int k) {
-		// the auto panel is sized for the devices that take part in THIS job
 		m->ctx[k]->cfg.shards_hint = n;
-		return sab_upload(m->ctx[k], seqs, meta, num, max);
+		const int r = install_set(m->ctx[k], ps, true);
+		m->ctx[k]->stats.upload_ms = now_ms() - t0;
+		return r;
 	});
 	if (rc == SAB_OK)
 		m->active = n;

@@ -170,15 +170,17 @@ template <> struct VOps<false> {
 
 // ---------------------------------------------------------------------------------------
 // int32 re-run of individual pairs whose int16 SW score may have wrapped.  One thread per
-// queued pair, two rolling rows (M and Y) in a per-thread global scratch.  Rare path
-// (needs a score > 32767 - max(S)); correctness over speed.
+// queued pair, two rolling rows (M and Y) in global scratch, interleaved across threads
+// (element c of thread t at [c * threads + t]: a warp's accesses coalesce).  Rare path (needs a
+// score > 32767 - max(S)); lists longer than ~2 % of a strip go to the int32 instantiation of
+// the strip kernel instead (sab_capi.cu: finish).
 // ---------------------------------------------------------------------------------------
 struct RerunParams {
 	DeviceSeqs seqs;
 	const unsigned long long *list;
 	const unsigned *count;
 	unsigned cap;
-	int32_t *scratch; // [threads][2][scratch_cols]
+	int32_t *scratch; // [2][scratch_cols][threads]
 	int scratch_cols;
 	const int32_t *sub25; // as TileParams (offset by -gapA)
 	int gapA, gapE;
@@ -194,8 +196,9 @@ __global__ void sab_rerun_sw_kernel(const RerunParams p)
 	const unsigned n = min(*p.count, p.cap);
 	const unsigned nthreads = gridDim.x * blockDim.x;
 	const unsigned me = blockIdx.x * blockDim.x + threadIdx.x;
-	int32_t *m = p.scratch + (int64_t)me * 2 * p.scratch_cols;
-	int32_t *y = m + p.scratch_cols;
+	int32_t *m = p.scratch + me;
+	int32_t *y = m + (int64_t)p.scratch_cols * nthreads;
+	const int64_t st = nthreads; // stride between consecutive columns of one thread's row
 	const int o = p.gapA, e = p.gapE;
 	const int NEG = INT32_MIN / 2;
 	for (unsigned k = me; k < n; k += nthreads) {
@@ -205,8 +208,8 @@ __global__ void sab_rerun_sw_kernel(const RerunParams p)
 		const uint8_t *qs = p.seqs.col_bytes + p.seqs.col_off[t];
 		const uint8_t *ss = p.seqs.col_bytes + p.seqs.col_off[s];
 		for (int c = 0; c <= Ls; c++) {
-			m[c] = 0;
-			y[c] = NEG;
+			m[c * st] = 0;
+			y[c * st] = NEG;
 		}
 		int best = 0;
 		for (int r = 0; r < Lq; r++) {
@@ -215,14 +218,15 @@ __global__ void sab_rerun_sw_kernel(const RerunParams p)
 			for (int c = 1; c <= Ls; c++) {
 				const int sub = srow[ss[c - 1]] + o; // sub25 carries -gapA
 				const int d = diag + sub;
+				const int up = m[c * st];
 				x = max(left + o, x + e);
-				const int yy = max(m[c] + o, y[c] + e);
+				const int yy = max(up + o, y[c * st] + e);
 				int v = max(d, 0);
 				v = max(v, x);
 				v = max(v, yy);
-				diag = m[c];
-				m[c] = v;
-				y[c] = yy;
+				diag = up;
+				m[c * st] = v;
+				y[c * st] = yy;
 				left = v;
 				best = max(best, v);
 			}
