@@ -87,3 +87,26 @@ def test_bad_arguments():
                             np.zeros(1, np.int32).ctypes.data, 0, 0, None, None) != capi.SAB_OK
     assert lib.sab_h5_write(b"/tmp/x.h5", (C.c_char_p * 1)(b"A"), 1,
                             np.zeros(1, np.int32).ctypes.data, 0, 10, None, None) == -1
+
+
+def test_reader_walks_a_file_written_by_libhdf5():
+    """Pins tests/h5min.py itself: a MATLAB v7.3 .mat file IS an HDF5 file written by libhdf5
+    (behind a 512-byte user block).  This one ships with SciPy's test data
+    (scipy/io/matlab/tests/data/testhdf5_7.4_GLNX86.mat, BSD licence; 4 KB, committed under
+    tests/golden/) and holds one variable: testdouble = 0, pi/4, ..., 2 pi.  The same reader
+    code that checks sab_h5_write's files must walk it: superblock v0 + base address, root
+    symbol-table entry, group B-tree, symbol-table node, local heap, v1 object header,
+    dataspace, datatype, contiguous layout, raw data."""
+    import numpy as np
+    from conftest import GOLDEN
+    import h5min
+    f = h5min.File(GOLDEN / "ext_libhdf5_matlab73_testdouble.mat", strict=False)
+    links = f.links()
+    assert list(links) == ["testdouble"]
+    data, info = f.read(links["testdouble"])
+    assert info["shape"] == (9, 1) and info["dtype"] == "<f8"
+    assert np.allclose(data.ravel(), np.arange(9) * np.pi / 4, rtol=0, atol=1e-15)
+    # and the strict mode used for our own files must refuse it (user block, foreign messages)
+    import pytest
+    with pytest.raises(AssertionError):
+        h5min.File(GOLDEN / "ext_libhdf5_matlab73_testdouble.mat")
