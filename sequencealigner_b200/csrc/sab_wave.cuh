@@ -121,8 +121,28 @@ __device__ __forceinline__ uint32_t cell(const CellK<METHOD, PACKED> &k, uint32_
 	return m;
 }
 
-// K = DP columns a warp holds in registers (strip width): 32 for long subjects, 16 for short
-// ones (less column padding, 5 resident blocks per SM instead of 4).
+#ifdef SAB_PICK_SWITCH
+// experiment: V[idx] for a block-uniform idx as a jump table instead of K compare/select pairs
+template <int K> __device__ __forceinline__ uint32_t pick_column(const uint32_t (&V)[K], const int idx)
+{
+	switch (idx) {
+#define SAB_PICK_CASE(i) \
+	case i:          \
+		return V[i < K ? i : 0];
+		SAB_PICK_CASE(0) SAB_PICK_CASE(1) SAB_PICK_CASE(2) SAB_PICK_CASE(3) SAB_PICK_CASE(4) SAB_PICK_CASE(5)
+		SAB_PICK_CASE(6) SAB_PICK_CASE(7) SAB_PICK_CASE(8) SAB_PICK_CASE(9) SAB_PICK_CASE(10) SAB_PICK_CASE(11)
+		SAB_PICK_CASE(12) SAB_PICK_CASE(13) SAB_PICK_CASE(14) SAB_PICK_CASE(15) SAB_PICK_CASE(16) SAB_PICK_CASE(17)
+		SAB_PICK_CASE(18) SAB_PICK_CASE(19) SAB_PICK_CASE(20) SAB_PICK_CASE(21) SAB_PICK_CASE(22) SAB_PICK_CASE(23)
+		SAB_PICK_CASE(24) SAB_PICK_CASE(25) SAB_PICK_CASE(26) SAB_PICK_CASE(27) SAB_PICK_CASE(28) SAB_PICK_CASE(29)
+		SAB_PICK_CASE(30) SAB_PICK_CASE(31)
+#undef SAB_PICK_CASE
+	}
+	return 0;
+}
+#endif
+
+// K = DP columns a warp holds in registers (strip width): 16..32 in steps of 2, chosen per subject
+// chunk by the host (sab_capi.cu: choose_widths); narrow strips fit 5 resident blocks per SM.
 template <int METHOD, bool PACKED, int K, int MINB>
 __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const TileParams p)
 {
@@ -429,19 +449,27 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 							const int cap0 = d_l0 - 1 - d_c0, cap1 = d_l1 - 1 - d_c0;
 							if (cap0 >= 0 && cap0 < K) {
 								uint32_t v = 0;
+#ifdef SAB_PICK_SWITCH
+								v = pick_column<K>(V, cap0);
+#else
 #pragma unroll
 								for (int c = 0; c < K; c++)
 									if (c == cap0)
 										v = V[c];
+#endif
 								sc0 = O::lo(v) + gS * (Lq + d_l0);
 								have0 = true;
 							}
 							if (PACKED && cap1 >= 0 && cap1 < K) {
 								uint32_t v = 0;
+#ifdef SAB_PICK_SWITCH
+								v = pick_column<K>(V, cap1);
+#else
 #pragma unroll
 								for (int c = 0; c < K; c++)
 									if (c == cap1)
 										v = V[c];
+#endif
 								sc1 = O::hi(v) + gS * (Lq + d_l1);
 								have1 = true;
 							}

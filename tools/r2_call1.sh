@@ -10,11 +10,11 @@ echo "pytest exit $?" >> $O/r2c1_pytest.txt
 tools/cell_peak > $O/r2c1_cell_peak.txt 2>&1
 tools/cell_peak_imm > $O/r2c1_cell_peak_imm.txt 2>&1
 { # default = per-chunk strip widths; --flags 8 / 16 = one width (32 / 16) for everything, as in round 1
-  tools/ab2.sh "default imm pref" --config c2
+  tools/ab2.sh "default imm pref pick" --config c2
   tools/ab2.sh "default" --config c2 --flags 8
   tools/ab2.sh "default imm pref" --config c3 --n 20000
   tools/ab2.sh "default" --config c3 --n 20000 --flags 8
-  tools/ab2.sh "default imm pref" --config c4 --n 40000 --no-filter
+  tools/ab2.sh "default imm pref pick" --config c4 --n 40000 --no-filter
   tools/ab2.sh "default" --config c4 --n 40000 --no-filter --flags 16
   tools/ab2.sh "default" --config c5 --n 12000
   tools/ab2.sh "default" --config c5 --n 12000 --flags 8
