@@ -81,6 +81,8 @@ enum sab_flags {
 	SAB_FLAG_TEST_RERUN_CAP = 64, /* testing: SW int16 re-run list of 4 entries (exercises the int32 re-sweep) */
 	SAB_FLAG_FILTER_SEQUENTIAL = 128, /* testing/tuning: sab_filter takes the panel-sequential path directly */
 	SAB_FLAG_TEST_FILTER_CAP = 256, /* testing: filter match list of 16 entries (exercises the fallback) */
+	SAB_FLAG_SERIAL_WIDTHS = 512, /* tuning: the per-width launches of a row strip run back to back on one stream
+				       * instead of concurrently on side streams */
 };
 
 typedef struct sab_config {
@@ -190,6 +192,16 @@ int sab_strip_info(const sab_ctx *ctx, int32_t strip, int32_t nshards, int32_t *
 		   int32_t *rows, int32_t *owner);
 
 int sab_get_stats(const sab_ctx *ctx, sab_stats *out);
+
+/* The strip kernels ship as one sm_100a device image (cubin) per register-strip width, embedded
+ * in the library; the per-lane gap constant of the cell update (GA: open - extend, SW: extend;
+ * two int16 lanes or one int32) is an IMMEDIATE operand that is written into the instruction
+ * words when a context first needs the kernel (csrc/sab_module.cu).  This returns a copy of the
+ * image of <method, packed, width> specialised for `gap_constant` -- what `cuobjdump -sass` of
+ * the running kernel would show -- and the number of instruction words that carry the constant
+ * (< 0: error).  out == NULL only reports *size and the kernel's (mangled) name.  Host only. */
+int sab_kernel_image(int method, int packed, int width, uint32_t gap_constant, unsigned char *out,
+		     size_t cap, size_t *size, char *kernel_name, size_t name_cap);
 
 /*
  * Every GPU of the box from one host process (what cuda_align needs: it is called once, on

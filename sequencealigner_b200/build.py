@@ -14,9 +14,13 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libseqalign_b200.so"
 PIPE_LIB = PKG / "libsab_pipepeak.so"
-SOURCES = ["sab_capi.cu", "sab_filter.cu", "sab_tables.cpp", "sab_h5.cpp"]
-WAVE_INST = "sab_wave_inst.cu"  # compiled once per register-strip width (-DSAB_K=<columns>)
-HEADERS = ["sab_kernels.cuh", "sab_wave.cuh", "sab_internal.h", "submat_tables.inc", "../../include/seqalign_b200.h"]
+SOURCES = ["sab_capi.cu", "sab_module.cu", "sab_filter.cu", "sab_tables.cpp", "sab_h5.cpp"]
+# the strip kernel: one cubin per register-strip width (-DSAB_K=<columns>), embedded in the library and
+# loaded by sab_module.cu, which overwrites the placeholder immediate below with the job's gap constant
+WAVE_INST = "sab_wave_inst.cu"
+LG_PLACEHOLDER = "0x5ab75ab7u"  # == sab::kLgPlaceholder (sab_kernels.cuh)
+HEADERS = ["sab_kernels.cuh", "sab_wave.cuh", "sab_internal.h", "sab_module.h", "submat_tables.inc",
+           "../../include/seqalign_b200.h"]
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC,-O3,-Wall,-Wno-unused-function", "-cudart", "shared",
@@ -58,8 +62,11 @@ def build_library(force: bool = False, verbose: bool = False, out: Path | None =
     objdir.mkdir(parents=True, exist_ok=True)
     base = [nvcc(), *NVCC_FLAGS, *defines] + (["-Xptxas=-v"] if verbose else [])
     jobs = [(base + ["-c", str(src), "-o", str(objdir / (src.stem + ".o"))]) for src in srcs]
-    jobs += [(base + [f"-DSAB_K={k}", "-c", str(CSRC / WAVE_INST), "-o", str(objdir / f"sab_wave_k{k}.o")])
-             for k in strip_widths()]
+    widths = strip_widths()
+    cubin_flags = [f for f in NVCC_FLAGS if f not in ("-Xcompiler", "-cudart", "shared") and not f.startswith("-fPIC")]
+    jobs += [([nvcc(), *cubin_flags, *defines] + (["-Xptxas=-v"] if verbose else []) +
+              [f"-DSAB_K={k}", f"-DSAB_LG_IMM={LG_PLACEHOLDER}", "-cubin", str(CSRC / WAVE_INST),
+               "-o", str(objdir / f"sab_wave_k{k}.cubin")]) for k in widths]
 
     def run(cmd):
         return subprocess.run(cmd, cwd=str(CSRC), capture_output=True, text=True)
@@ -71,7 +78,14 @@ def build_library(force: bool = False, verbose: bool = False, out: Path | None =
             print(" ".join(cmd[-4:]), r.stdout, r.stderr, sep="\n")
         if r.returncode:
             raise subprocess.CalledProcessError(r.returncode, cmd, r.stdout, r.stderr)
-    objs = [c[-1] for c in jobs]
+    # the device images become read-only data of the library (symbols sab_cubin_k<K> / _end)
+    asm = objdir / "sab_images.S"
+    asm.write_text("\t.section .rodata\n" + "".join(
+        f"\t.balign 64\n\t.global sab_cubin_k{k}\nsab_cubin_k{k}:\n\t.incbin \"{objdir / f'sab_wave_k{k}.cubin'}\"\n"
+        f"\t.global sab_cubin_k{k}_end\nsab_cubin_k{k}_end:\n" for k in widths) +
+        "\t.section .note.GNU-stack,\"\",@progbits\n")
+    subprocess.run(["gcc", "-c", "-fPIC", str(asm), "-o", str(objdir / "sab_images.o")], check=True)
+    objs = [c[-1] for c in jobs[:len(srcs)]] + [str(objdir / "sab_images.o")]
     subprocess.run([nvcc(), "-shared", "-cudart", "shared", "-gencode", "arch=compute_100a,code=sm_100a",
                     "-o", str(out), *objs, "-lz"], check=True, cwd=str(CSRC))
     return out

@@ -21,6 +21,7 @@ SAB_FLAG_ORDERED = 32
 SAB_FLAG_TEST_RERUN_CAP = 64
 SAB_FLAG_FILTER_SEQUENTIAL = 128
 SAB_FLAG_TEST_FILTER_CAP = 256
+SAB_FLAG_SERIAL_WIDTHS = 512
 STATUS = {0: "SAB_OK", -1: "SAB_ERR_ARG", -2: "SAB_ERR_NODEVICE", -3: "SAB_ERR_CUDA",
           -4: "SAB_ERR_NOMEM", -5: "SAB_ERR_STATE", -6: "SAB_ERR_OVERFLOW"}
 
@@ -78,6 +79,8 @@ SYMBOLS = {
                                   C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                   C.POINTER(C.c_int32)]),
     "sab_get_stats": (C.c_int, [C.c_void_p, C.POINTER(SabStats)]),
+    "sab_kernel_image": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t,
+                                   C.POINTER(C.c_size_t), C.c_char_p, C.c_size_t]),
     "sab_multi_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(SabConfig), C.c_int32]),
     "sab_multi_destroy": (None, [C.c_void_p]),
     "sab_multi_last_error": (C.c_char_p, [C.c_void_p]),

@@ -10,9 +10,9 @@
 //
 // There is no CPU fallback in this file: without a usable sm_100 device every
 // compute entry point returns SAB_ERR_NODEVICE / SAB_ERR_CUDA.
-#include "sab_internal.h"
 #define SAB_WITH_RERUN_KERNEL
-#include "sab_kernels.cuh"
+#include "sab_module.h"
+#include "sab_wave.cuh" // WaveSmem<K> (shared-memory size per width); the kernels themselves are device images
 
 #include <algorithm>
 #include <atomic>
@@ -62,7 +62,13 @@ struct StripBuf {
 	size_t rerun_scratch_cap = 0;
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev_start = nullptr, ev_done = nullptr;
+	// the launches of one strip (one per register-strip width in use) are independent: they run on
+	// side streams forked from `stream`, so the tail of one overlaps the start of the next
+	cudaStream_t side[15] = { nullptr };
+	cudaEvent_t ev_fork = nullptr, ev_join[15] = { nullptr };
 };
+
+constexpr int kCounterWords = 32; // [1] re-run count, [4 + w] work counter of the width-w launch
 
 } // namespace
 
@@ -94,9 +100,10 @@ struct sab_ctx {
 	cudaEvent_t ev_copy[2] = { nullptr, nullptr };
 	cudaEvent_t ev_span[2] = { nullptr, nullptr }; // first kernel start / last kernel end
 	struct Variant { // [method][packed][width index], set up on first use (wave_variant)
-		void (*fn)(const sab::TileParams) = nullptr;
+		void *fn = nullptr; // CUfunction of the specialised image (sab_module.cu)
 		int smem = 0, grid = 0;
 	} variants[3][2][16];
+	void *modules = nullptr; // sab_module.cu cache of this context's loaded images
 	bool sw_prefer_int32 = false; // a strip's re-run list overflowed: later risky strips start in int32
 	sab_stats stats{};
 	// sab_filter.cu keeps its device buffers here (released by sab_destroy)
@@ -150,14 +157,14 @@ int ensure(sab_ctx *ctx, void **p, size_t *cap, size_t need, size_t elem)
 // of a global 32 or 16.  Widest first; int32 strips use the first and the last entry only.
 struct WidthInfo {
 	int k;
-	sab::wave_kernel_t (*get)(int method, bool packed, int *smem_bytes, int *minb);
+	int smem; // sizeof(WaveSmem<K>)
 };
-#define SAB_WIDTH_ENTRY(K) { K, sab::wave_kernel_k##K },
+#define SAB_WIDTH_ENTRY(K) { K, (int)sizeof(sab::WaveSmem<K>) },
 constexpr WidthInfo kWidths[] = { SAB_WIDTHS(SAB_WIDTH_ENTRY) };
 #undef SAB_WIDTH_ENTRY
 constexpr int kNumWidths = (int)(sizeof(kWidths) / sizeof(kWidths[0]));
 constexpr int kWidest = 0, kNarrowest = kNumWidths - 1;
-static_assert(kNumWidths <= 16 && kWidths[kWidest].k == sab::kStrip, "width table");
+static_assert(kNumWidths <= 15 && kWidths[kWidest].k == sab::kStrip, "width table");
 
 // Relative cost of one DP column in a strip of width K: a step carries the same bookkeeping
 // (~165 instructions) whatever its width.  Calibrated on B200: a 16-column step costs 5.5 % more
@@ -169,20 +176,33 @@ inline double column_cost(int k)
 
 typedef sab_ctx::Variant WaveVariant;
 
-// One kernel variant, set up on first use (dynamic shared memory attribute + occupancy query:
-// ~1 ms each; a job launches a handful of the 33).
+// The per-lane gap constant of the add-max ops (sab_wave.cuh: CellK::lG), written into the image
+// as an immediate operand: GA o - e, SW e; NW has none.
+uint32_t lane_gap_constant(const sab_ctx *ctx, bool packed)
+{
+	const int v = ctx->cfg.method == SAB_GA ? ctx->gapA - ctx->gapE : ctx->gapE;
+	return packed ? ((uint32_t)v & 0xffffu) * 0x10001u : (uint32_t)v;
+}
+
+// One kernel variant, set up on first use: its device image is specialised for this context's gap
+// constant and loaded (sab_module.cu, ~1 ms; a job uses a handful of the 24).
 int wave_variant(sab_ctx *ctx, int method, bool packed, int widx, WaveVariant *out)
 {
 	WaveVariant &v = ctx->variants[method][packed][widx];
 	if (!v.fn) {
-		int minb = 0, occ = 0;
-		sab::wave_kernel_t fn = kWidths[widx].get(method, packed, &v.smem, &minb);
-		if (!fn)
-			return fail(ctx, SAB_ERR_STATE, "no int32 kernel of width %d", kWidths[widx].k);
-		CU(cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, v.smem));
-		CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)fn, sab::kWaveThreads, v.smem));
+		const int k = kWidths[widx].k;
+		if (!packed && widx != kWidest && widx != kNarrowest)
+			return fail(ctx, SAB_ERR_STATE, "no int32 kernel of width %d", k);
+		int occ = 0;
+		void *fn = nullptr;
+		std::string err;
+		const int rc = sab_module_get(&ctx->modules, method, packed, k, lane_gap_constant(ctx, packed),
+					      kWidths[widx].smem, &fn, &occ, &err);
+		if (rc)
+			return fail(ctx, rc, "%s", err.c_str());
 		if (occ < 1)
 			return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
+		v.smem = kWidths[widx].smem;
 		v.grid = occ * ctx->sm_count;
 		v.fn = fn;
 	}
@@ -538,7 +558,8 @@ int sab_create(sab_ctx **out, const sab_config *cfg)
 		CU(cudaStreamCreateWithFlags(&b.stream, cudaStreamNonBlocking));
 		CU(cudaEventCreate(&b.ev_start));
 		CU(cudaEventCreate(&b.ev_done));
-		CU(cudaMalloc(&b.counter, 4 * sizeof(unsigned)));
+		CU(cudaMalloc(&b.counter, kCounterWords * sizeof(unsigned)));
+		CU(cudaEventCreateWithFlags(&b.ev_fork, cudaEventDisableTiming));
 		CU(cudaEventCreateWithFlags(&ctx->ev_copy[i], cudaEventDisableTiming));
 	}
 	CU(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
@@ -556,6 +577,7 @@ void sab_destroy(sab_ctx *ctx)
 		cudaDeviceSynchronize();
 		if (ctx->filter_state && ctx->filter_free)
 			ctx->filter_free(ctx->filter_state);
+		sab_module_release(ctx->modules);
 		free_seqs(ctx);
 		free_bufs(ctx);
 		cudaFree(ctx->d_sub25);
@@ -569,6 +591,14 @@ void sab_destroy(sab_ctx *ctx)
 				cudaEventDestroy(b.ev_start);
 			if (b.ev_done)
 				cudaEventDestroy(b.ev_done);
+			if (b.ev_fork)
+				cudaEventDestroy(b.ev_fork);
+			for (auto s : b.side)
+				if (s)
+					cudaStreamDestroy(s);
+			for (auto e : b.ev_join)
+				if (e)
+					cudaEventDestroy(e);
 			if (ctx->stage[i])
 				cudaFreeHost(ctx->stage[i]);
 			if (ctx->ev_copy[i])
@@ -1055,9 +1085,17 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 	const bool test_cap = ctx->cfg.flags & SAB_FLAG_TEST_RERUN_CAP;
 	const unsigned rerun_cap = test_cap ? 4u : kRerunCap;
 
-	auto launch = [&](const Strip &st, StripBuf &b) -> int {
+	auto launch = [&](const Strip &st_in, StripBuf &b) -> int {
+		Strip st = st_in;
 		const bool packed = st.packed;
 		const int a1 = st.a0 + st.an;
+		// a packed strip that is swept (again) in int32 -- re-run list overflow, sw_prefer_int32 --
+		// arrives without a fixed width: the int32 kernel exists at the widest and narrowest only
+		if (!packed && (st.widx_fixed < 0 || (st.widx_fixed != kWidest && st.widx_fixed != kNarrowest)))
+			st.widx_fixed = (double)ctx->pad16_prefix[a1] * column_cost(16) <
+							(double)ctx->pad32_prefix[a1] * column_cost(32) ?
+						kNarrowest :
+						kWidest;
 		const size_t blk_elems = (size_t)(tri(a1) - tri(st.a0));
 		int rc = ensure(ctx, (void **)&b.blk, &b.blk_cap, std::max<size_t>(blk_elems, 1), sizeof(int32_t));
 		if (rc)
@@ -1097,8 +1135,14 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 					return rc;
 				max_grid = std::max(max_grid, var[w].grid);
 			}
+		int nlaunch = 0;
+		for (int w = 0; w < kNumWidths; w++)
+			nlaunch += first[w + 1] > first[w];
+		const bool serial = ctx->cfg.flags & SAB_FLAG_SERIAL_WIDTHS;
 		const size_t bnd_block = (size_t)bnd_rows * 32;
-		rc = ensure(ctx, (void **)&b.bnd, &b.bnd_cap, bnd_block * max_grid, sizeof(uint2));
+		// concurrent launches need a wrap-around boundary region each (indexed by blockIdx)
+		const size_t bnd_launch = bnd_block * max_grid;
+		rc = ensure(ctx, (void **)&b.bnd, &b.bnd_cap, bnd_launch * (serial ? 1 : std::max(1, nlaunch)), sizeof(uint2));
 		if (rc)
 			return rc;
 		TileParams p{};
@@ -1123,24 +1167,46 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 		p.rerun_list = b.rerun_list;
 		p.rerun_count = b.counter + 1;
 		p.rerun_cap = rerun_cap;
-		CU(cudaMemsetAsync(b.counter, 0, 4 * sizeof(unsigned), b.stream));
+		CU(cudaMemsetAsync(b.counter, 0, kCounterWords * sizeof(unsigned), b.stream));
 		if (S.launches == 0)
 			CU(cudaEventRecord(ctx->ev_span[0], b.stream));
 		CU(cudaEventRecord(b.ev_start, b.stream));
-		bool first_launch = true;
-		for (int w = 0; w < kNumWidths; w++) { // one launch per width in use, back to back
+		if (nlaunch > 1 && !serial)
+			CU(cudaEventRecord(b.ev_fork, b.stream));
+		// One launch per width in use (widest first).  They touch disjoint subject chunks of the
+		// strip buffer, so all but the first go to side streams: the persistent blocks of launch
+		// k + 1 move onto the SMs as those of launch k run out of work items.
+		int li = 0;
+		for (int w = 0; w < kNumWidths; w++) {
 			p.nsc = first[w + 1] - first[w];
 			if (p.nsc <= 0)
 				continue;
 			p.chunk_ids = st.widx_fixed >= 0 ? nullptr : b.chunk_ids + first[w];
-			if (!first_launch) // the work counter restarts, the re-run count accumulates
-				CU(cudaMemsetAsync(b.counter, 0, sizeof(unsigned), b.stream));
-			first_launch = false;
-			var[w].fn<<<var[w].grid, sab::kWaveThreads, var[w].smem, b.stream>>>(p);
-			CU(cudaGetLastError());
+			p.counter = b.counter + 4 + w; // the re-run count (counter[1]) is shared and accumulates
+			cudaStream_t s = b.stream;
+			if (li > 0 && !serial) {
+				if (!b.side[li]) {
+					CU(cudaStreamCreateWithFlags(&b.side[li], cudaStreamNonBlocking));
+					CU(cudaEventCreateWithFlags(&b.ev_join[li], cudaEventDisableTiming));
+				}
+				s = b.side[li];
+				CU(cudaStreamWaitEvent(s, b.ev_fork, 0));
+				p.bnd = b.bnd + bnd_launch * li;
+			}
+			{
+				std::string err;
+				if (sab_module_launch(var[w].fn, var[w].grid, var[w].smem, s, &p, &err))
+					return fail(ctx, SAB_ERR_CUDA, "%s", err.c_str());
+			}
+			if (s != b.stream)
+				CU(cudaEventRecord(b.ev_join[li], s));
 			S.launches++;
 			S.width_launches[w]++;
+			li++;
 		}
+		if (!serial)
+			for (int k = 1; k < li; k++)
+				CU(cudaStreamWaitEvent(b.stream, b.ev_join[k], 0));
 		CU(cudaEventRecord(b.ev_done, b.stream));
 		S.tiles++;
 		if (!packed)

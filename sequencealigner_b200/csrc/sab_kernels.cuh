@@ -84,14 +84,16 @@ struct TileParams {
 	unsigned rerun_cap;
 };
 
-typedef void (*wave_kernel_t)(const TileParams);
-
-// Register-strip widths the strip kernel is built for (sab_wave_inst.cu, one translation unit
-// per width) and the getters those units export.
+// Register-strip widths the strip kernel is built for: one device image per width (sab_wave_inst.cu,
+// compiled to a cubin and embedded by build.py; loaded and specialised by sab_module.cu).
 #define SAB_WIDTHS(X) X(32) X(30) X(28) X(26) X(24) X(22) X(20) X(18) X(16)
-#define SAB_DECLARE_WIDTH(K) wave_kernel_t wave_kernel_k##K(int method, bool packed, int *smem_bytes, int *minb);
-SAB_WIDTHS(SAB_DECLARE_WIDTH)
-#undef SAB_DECLARE_WIDTH
+// resident blocks per SM the register budget allows: 2K registers hold the strip itself
+constexpr int wave_minb(int k)
+{
+	return k <= 20 ? 5 : 4;
+}
+// placeholder of the per-lane gap constant in the built images (sab_module.cu overwrites it)
+constexpr uint32_t kLgPlaceholder = 0x5ab75ab7u;
 
 // ---------------------------------------------------------------------------------------
 // Vector ops: two int16 lanes per register (Blackwell DPX) or one int32.

@@ -147,3 +147,57 @@ def test_filter_resolve_is_the_sequential_recurrence(oracle_mod):
         got = filter_resolve(store.num, pairs)
         assert np.array_equal(got, oracle_mod.filter_lost(store, thr)), thr
     assert not filter_resolve(5, np.zeros(0, np.uint64)).any()
+
+
+@pytest.mark.parametrize("method,packed,width,value", [
+    (1, 1, 32, 0xfff7fff7),  # GA int16x2: lane(o - e) = -9 in both lanes (-s 10 -e 1)
+    (2, 1, 30, 0xffffffff),  # SW int16x2: lane(e) = -1
+    (2, 0, 16, 0xfffffffe),  # SW int32: e = -2
+    (1, 0, 32, 0xffffff9c),  # GA int32: o - e = -100
+    (0, 1, 24, 0),           # NW has no gap constant in its add-max ops
+])
+def test_kernel_images_are_specialised_by_immediate_only(tmp_path, method, packed, width, value):
+    """The strip kernels ship as cubins with a placeholder immediate (csrc/sab_module.cu).  Writing a
+    job's gap constant must change exactly the immediate operands of VIADDMNMX instructions of ONE
+    kernel and nothing else -- checked on the disassembly, which needs no GPU."""
+    import shutil
+    import subprocess
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    lib = capi.load()
+    size = C.c_size_t(0)
+    name = C.create_string_buffer(200)
+    assert lib.sab_kernel_image(method, packed, width, value, None, 0, C.byref(size), name, 200) == 0
+    assert b"sab_wave_kernel" in name.value and size.value > 100000
+    placeholder = 0x5ab75ab7
+
+    def sass(val):
+        buf = (C.c_ubyte * size.value)()
+        sites = lib.sab_kernel_image(method, packed, width, val, buf, size.value, C.byref(size), name, 200)
+        path = tmp_path / f"img_{val:x}.cubin"
+        path.write_bytes(bytes(buf))
+        txt = subprocess.run(["cuobjdump", "-sass", "-fun", name.value.decode(), str(path)],
+                             capture_output=True, text=True, check=True).stdout
+        ins = [l.split("*/", 1)[1].split(";")[0].strip() for l in txt.splitlines()
+               if re.match(r"\s+/\*[0-9a-f]{4,}\*/", l)]
+        return sites, ins, bytes(buf)
+
+    sites0, ins0, raw0 = sass(placeholder)  # identity patch: the image as built
+    sites1, ins1, raw1 = sass(value)
+    assert sites0 == sites1 and len(ins0) == len(ins1) > 1000
+    if method == 0:
+        assert sites1 == 0 and raw0 == raw1
+        return
+    # GA packed: 2 add-max ops per cell pair in the 8-, 4-, 2- and 1-row blocks; SW: 8-row block only
+    # (SW int32 keeps the vertical gap in __viaddmax_s32_relu with the raw extend: one site per cell)
+    rows = 15 if method == 1 else 8
+    assert sites1 == (1 if (method == 2 and not packed) else 2) * width * rows
+    diff = [(a, b) for a, b in zip(ins0, ins1) if a != b]
+    assert len(diff) == sites1
+    for a, b in diff:
+        assert a.startswith("VIADDMNMX") and f"0x{placeholder:x}" in a
+        assert b == a.replace(f"0x{placeholder:x}", f"0x{value:x}")
+    assert not any(f"0x{placeholder:x}" in b for b in ins1)
+    # every other kernel of the image still carries its placeholder (they are specialised separately)
+    assert sum(x != y for x, y in zip(raw0, raw1)) <= 4 * sites1
+    assert lib.sab_kernel_image(method, 0, 24, value, None, 0, C.byref(size), name, 200) < 0

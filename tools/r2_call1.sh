@@ -5,7 +5,7 @@ O=gpurun_out
 mkdir -p $O
 { nproc; free -g; df -h /tmp /dev/shm .; python -c "import h5py; print('h5py', h5py.__version__)"; which h5dump h5ls h5cc;
   nvidia-smi -L; lscpu | grep -E "Model name|Socket|Core|Thread|MHz"; nvidia-smi --query-gpu=clocks.sm,clocks.max.sm,power.limit --format=csv; } > $O/r2c1_box.txt 2>&1
-timeout 1800 python -m pytest tests -m gpu -x -q -p no:cacheprovider > $O/r2c1_pytest.txt 2>&1
+timeout 1800 python -m pytest tests -m gpu -q -p no:cacheprovider > $O/r2c1_pytest.txt 2>&1
 echo "pytest exit $?" >> $O/r2c1_pytest.txt
 tools/cell_peak > $O/r2c1_cell_peak.txt 2>&1
 tools/cell_peak_imm > $O/r2c1_cell_peak_imm.txt 2>&1
