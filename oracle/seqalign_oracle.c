@@ -10,7 +10,7 @@
  * Parity pin: the reference ships no golden vectors, so
  * this restatement is pinned against the UNMODIFIED reference CPU sources
  * compiled into oracle/_ref/seqalign (see oracle/Makefile) -- in this container
- * by tests/test_oracle_vs_reference.py, and everywhere through the committed
+ * by tests/test_oracle.py, and everywhere through the committed
  * fixtures under tests/golden/ that were produced by that binary
  * (tools/make_golden.py).
  *

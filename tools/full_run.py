@@ -39,7 +39,13 @@ def open_sink(kind: str, nbytes: int, directory: str | None):
     a tmp file when the FULL matrix would not fit in 3/4 of MemAvailable (output.c:36)."""
     if kind == "ram":
         return np.zeros(nbytes // 4, dtype=np.int32), (lambda: 0.0), "anonymous memory"
-    d = directory or ("/tmp" if os.path.isdir("/tmp") else None)
+    # the reference uses /tmp (os.c:111); when its file system cannot hold the matrix, the next
+    # candidate with room (a tmpfs mapping is still a file-backed MAP_SHARED sink, without write-back)
+    import shutil
+    cands = [directory] if directory else ["/tmp", "/var/tmp", os.getcwd(), "/dev/shm"]
+    d = next((c for c in cands if c and os.path.isdir(c) and shutil.disk_usage(c).free > nbytes * 1.05), None)
+    if d is None:
+        raise SystemExit(f"no directory with {nbytes / 2**30:.0f} GiB free for the sink file: {cands}")
     fd = os.open(d, os.O_TMPFILE | os.O_RDWR, 0o600)  # os.c:111: unnamed file in /tmp
     os.ftruncate(fd, nbytes)
     mm = mmap.mmap(fd, nbytes, flags=mmap.MAP_SHARED)
@@ -56,7 +62,11 @@ def open_sink(kind: str, nbytes: int, directory: str | None):
         dt = time.perf_counter() - t0
         os.close(fd)
         return dt
-    return view, close, f"O_TMPFILE in {d}, MAP_SHARED, MADV_RANDOM|MADV_HUGEPAGE"
+    real = os.path.realpath(d)
+    mounts = [l.split() for l in open("/proc/mounts")]
+    fs = max((m for m in mounts if real == m[1] or real.startswith(m[1].rstrip("/") + "/")),
+             key=lambda m: len(m[1]), default=[None, None, "?"])[2]
+    return view, close, f"O_TMPFILE in {d} ({fs}), MAP_SHARED, MADV_RANDOM|MADV_HUGEPAGE"
 
 
 def main():

@@ -23,6 +23,9 @@ echo "pytest exit $?" >> $O/r2c2_pytest.txt
   tools/ab2.sh "default" --config c2 --emulate-shards 8 --panel 1792
   tools/ab2.sh "default" --config c2 --emulate-shards 8 --panel 1792 --flags 8
   tools/ab2.sh "default" --config c2 --emulate-shards 8 --panel 3584 --flags 8
+  tools/ab2.sh "default" --config c2 --panel 2560
+  tools/ab2.sh "default" --config c2 --panel 2560 --flags 8
+  tools/ab2.sh "default" --config c2 --panel 3328 --flags 8
 } > $O/r2c2_ab.txt 2>&1
 timeout 900 python bench.py > $O/r2c2_bench_c2.json 2> $O/r2c2_bench_c2.err
 # counters behind "3 DPX + 1 IMAD + 1 LDS costs 7.5 clk, not 6": the bare 8 x 32 block, register vs immediate gap constant
