@@ -83,7 +83,8 @@ struct sab_ctx {
 	int32_t *d_sub25 = nullptr;
 	// sequence store (host copies of the small tables)
 	bool uploaded = false;
-	int32_t num = 0, max_len = 0, panel = 0;
+	int32_t num = 0, max_len = 0;
+	std::vector<int32_t> panel_start; // [npanels + 1] row boundaries of the row strips (panel_bounds)
 	std::vector<int32_t> slot_len, slot_orig;
 	std::vector<int64_t> len_prefix; // len_prefix[s] = sum of slot_len[0..s)
 	std::vector<int64_t> pad16_prefix, pad32_prefix; // same, lengths rounded up to 16 / 32 columns
@@ -345,15 +346,64 @@ bool int16_safe(const sab_ctx *c, int lq, int ls)
 	return low >= -32000 && high <= 32000;
 }
 
-// Panel height: a multiple of the query block; several strips per shard so the LPT
-// assignment balances, capped so a block's 128 length-sorted queries stay similar.
-int auto_panel(int num, int panel, int shards_hint)
+// Panels = ranges of consecutive ORIGINAL indices = the rows of one row strip.  `start` gets the
+// npanels + 1 boundaries (multiples of 32: a 32-slot query group never straddles a panel).
+//   panel > 0         uniform height, as asked for.
+//   static shards     (sab_align_shard: every rank runs the strips a deterministic plan gives it)
+//                     EQUAL-COST strips: rows [a0, a1) cost (P[a1]^2 - P[a0]^2) / 2 cells, P = prefix
+//                     sum of the lengths, so the boundaries sit where P^2 crosses k / E of its final
+//                     value: a tall strip at the top of the triangle, thin ones at the bottom, all
+//                     with the same number of cells (and, near enough, of pairs: equal buffers).
+//                     E = 2 per shard (4 for a single shard: the last strip's write-back is exposed),
+//                     more when a strip would exceed 2^29 scores (2 GiB per strip buffer).  Every
+//                     launch then has the same amount of work however many shards there are --
+//                     uniform 6-per-shard panels left the strips of an 8-GPU job at 640 rows and the
+//                     per-GPU rate 5-9 % below the 1-GPU one -- and the longest-processing-time
+//                     assignment is balanced by construction (E is a multiple of the shards).
+//   dynamic           (sab_multi_*: devices pull strips from a shared cursor, costliest first)
+//                     uniform height, ~6 strips per device: costs then FALL linearly along the issue
+//                     order, which is what keeps the tail of a dynamically scheduled job short.
+void panel_bounds(const std::vector<int64_t> &P /* [num + 1] prefix sums of the lengths, original order */,
+		  int num, int panel, int shards_hint, bool dynamic, std::vector<int32_t> &start)
 {
-	if (panel > 0)
-		return panel;
-	const int want = shards_hint > 0 ? 6 * shards_hint : 6;
-	panel = (num / want + kPanelQuantum - 1) / kPanelQuantum * kPanelQuantum;
-	return std::max(2 * kPanelQuantum, std::min(panel, 4096));
+	start.clear();
+	start.push_back(0);
+	const int shards = std::max(1, shards_hint);
+	if (panel <= 0 && dynamic) {
+		panel = (num / (6 * shards) + kPanelQuantum - 1) / kPanelQuantum * kPanelQuantum;
+		panel = std::max(2 * kPanelQuantum, std::min(panel, 4096));
+	}
+	if (panel > 0) {
+		for (int a = panel; a < num; a += panel)
+			start.push_back(a);
+		start.push_back(num);
+		return;
+	}
+	const int unit = shards > 1 ? 2 * shards : 4;
+	const int64_t pairs = tri(num);
+	const int E = (int)((std::max<int64_t>(1, (pairs + (1ll << 29) - 1) >> 29) + unit - 1) / unit) * unit;
+	const int minh = 64; // two query groups
+	const double T2 = (double)P[num] * (double)P[num] / E; // cost of a strip in units of P^2 = 2 * cells
+	std::vector<int32_t> cuts; // built from the bottom of the triangle upwards
+	int a1 = num;
+	for (int k = 0; k < E - 1 && a1 > 0; k++) {
+		const double lo2 = (double)P[a1] * (double)P[a1] - T2;
+		int a0 = 0;
+		if (lo2 > 0) {
+			a0 = (int)(std::lower_bound(P.begin(), P.begin() + a1, (int64_t)std::sqrt(lo2)) - P.begin());
+			a0 = (a0 + 16) / 32 * 32;
+		}
+		a0 = std::max(0, std::min(a0, a1 - minh));
+		if (a0 < minh)
+			a0 = 0;
+		cuts.push_back(a0);
+		a1 = a0;
+	}
+	for (int k = (int)cuts.size() - 1; k >= 0; k--)
+		if (cuts[k] > 0)
+			start.push_back(cuts[k]);
+	start.push_back(num);
+	start.erase(std::unique(start.begin(), start.end()), start.end());
 }
 
 // Longest-processing-time assignment of strips (cost ~ cells) to shards; deterministic.
@@ -621,8 +671,8 @@ namespace {
 // The sequence set in its two device layouts, packed once on the host;
 // sab_multi_upload hands the same object to every device.
 struct PackedSet {
-	int32_t num = 0, max_len = 0, panel = 0;
-	std::vector<int32_t> slot_len, slot_orig, panel_maxlen;
+	int32_t num = 0, max_len = 0;
+	std::vector<int32_t> slot_len, slot_orig, panel_maxlen, panel_start;
 	std::vector<int64_t> col_off, grp_off, len_prefix, pad16_prefix, pad32_prefix;
 	std::vector<uint8_t> col_bytes;
 	std::vector<uint32_t> rowpack;
@@ -650,8 +700,14 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 
 	// Panels: contiguous ranges of ORIGINAL indices, so a row strip of the output is
 	// one contiguous run of the packed-triangular matrix.
-	const int panel = auto_panel(num, ctx->cfg.panel, ctx->cfg.shards_hint);
-	const int npanels = (num + panel - 1) / panel;
+	{
+		std::vector<int64_t> P((size_t)num + 1, 0);
+		for (int32_t k = 0; k < num; k++)
+			P[k + 1] = P[k] + meta[k].len;
+		panel_bounds(P, num, ctx->cfg.panel, ctx->cfg.shards_hint, ctx->cfg.flags & SAB_FLAG_INTERNAL_DYNAMIC,
+			     ps.panel_start);
+	}
+	const int npanels = (int)ps.panel_start.size() - 1;
 
 	// Length binning: stable sort by length inside each panel -> slots.
 	std::vector<int32_t> &slot_orig = ps.slot_orig, &slot_len = ps.slot_len;
@@ -660,8 +716,8 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 	std::iota(slot_orig.begin(), slot_orig.end(), 0);
 	ps.panel_maxlen.assign(npanels, 0);
 	for (int p = 0; p < npanels; p++) {
-		auto b = slot_orig.begin() + (size_t)p * panel;
-		auto e = slot_orig.begin() + std::min<size_t>((size_t)(p + 1) * panel, num);
+		auto b = slot_orig.begin() + ps.panel_start[p];
+		auto e = slot_orig.begin() + ps.panel_start[p + 1];
 		std::stable_sort(b, e, [&](int32_t x, int32_t y) { return meta[x].len < meta[y].len; });
 		ps.panel_maxlen[p] = meta[*(e - 1)].len;
 	}
@@ -737,7 +793,6 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 	});
 	ps.num = num;
 	ps.max_len = real_max;
-	ps.panel = panel;
 	return SAB_OK;
 }
 
@@ -774,7 +829,6 @@ int install_set(sab_ctx *ctx, PackedSet &ps, bool keep)
 					 ps.col_bytes.size() + ps.rowpack.size() * sizeof(uint32_t));
 	ctx->num = num;
 	ctx->max_len = ps.max_len;
-	ctx->panel = ps.panel;
 	if (keep) {
 		ctx->slot_len = ps.slot_len;
 		ctx->slot_orig = ps.slot_orig;
@@ -782,6 +836,7 @@ int install_set(sab_ctx *ctx, PackedSet &ps, bool keep)
 		ctx->pad16_prefix = ps.pad16_prefix;
 		ctx->pad32_prefix = ps.pad32_prefix;
 		ctx->panel_maxlen = ps.panel_maxlen;
+		ctx->panel_start = ps.panel_start;
 	} else {
 		ctx->slot_len.swap(ps.slot_len);
 		ctx->slot_orig.swap(ps.slot_orig);
@@ -789,6 +844,7 @@ int install_set(sab_ctx *ctx, PackedSet &ps, bool keep)
 		ctx->pad16_prefix.swap(ps.pad16_prefix);
 		ctx->pad32_prefix.swap(ps.pad32_prefix);
 		ctx->panel_maxlen.swap(ps.panel_maxlen);
+		ctx->panel_start.swap(ps.panel_start);
 	}
 	ctx->sw_prefer_int32 = false;
 	ctx->uploaded = true;
@@ -836,8 +892,7 @@ struct Strip {
 // of strips to shards (deterministic: every rank computes the same plan).
 void plan_strips(const sab_ctx *ctx, int nshards, std::vector<Strip> &strips, std::vector<int> &owner)
 {
-	const int num = ctx->num, panel = ctx->panel;
-	const int npanels = (num + panel - 1) / panel;
+	const int npanels = (int)ctx->panel_start.size() - 1;
 	const bool force32 = ctx->cfg.flags & SAB_FLAG_FORCE_INT32;
 	const bool force16 = ctx->cfg.flags & SAB_FLAG_FORCE_INT16;
 	strips.assign(npanels, Strip{});
@@ -845,8 +900,8 @@ void plan_strips(const sab_ctx *ctx, int nshards, std::vector<Strip> &strips, st
 	for (int p = 0; p < npanels; p++) {
 		Strip &s = strips[p];
 		s.panel = p;
-		s.a0 = p * panel;
-		s.an = std::min(panel, num - s.a0);
+		s.a0 = ctx->panel_start[p];
+		s.an = ctx->panel_start[p + 1] - s.a0;
 		run_max = std::max(run_max, ctx->panel_maxlen[p]);
 		s.lq = ctx->panel_maxlen[p];
 		s.ls = run_max;
@@ -1394,23 +1449,23 @@ int sab_plan_strips(const sab_meta *meta, int32_t num, int32_t panel, int32_t ns
 {
 	if (!meta || num < 2 || nshards < 1 || panel < 0 || panel % kPanelQuantum)
 		return SAB_ERR_ARG;
-	panel = auto_panel(num, panel, nshards);
-	const int npanels = (num + panel - 1) / panel;
+	std::vector<int64_t> P((size_t)num + 1, 0);
+	for (int32_t k = 0; k < num; k++)
+		P[k + 1] = P[k] + meta[k].len;
+	std::vector<int32_t> start;
+	panel_bounds(P, num, panel, nshards, false, start);
+	const int npanels = (int)start.size() - 1;
 	if (npanels > max_strips)
 		return npanels;
 	std::vector<double> cost(npanels);
-	double before = 0;
 	for (int p = 0; p < npanels; p++) {
-		const int a0 = p * panel, an = std::min(panel, num - a0);
-		double lq = 0;
-		for (int k = a0; k < a0 + an; k++)
-			lq += meta[k].len;
-		cost[p] = lq * (before + 0.5 * lq);
-		before += lq;
+		const int a0 = start[p], a1 = start[p + 1];
+		const double lq = (double)(P[a1] - P[a0]);
+		cost[p] = lq * ((double)P[a0] + 0.5 * lq);
 		if (row0)
 			row0[p] = a0;
 		if (rows)
-			rows[p] = an;
+			rows[p] = a1 - a0;
 	}
 	std::vector<int> owner;
 	lpt_assign(cost, nshards, owner);
@@ -1424,7 +1479,7 @@ int sab_strip_count(const sab_ctx *ctx)
 {
 	if (!ctx || !ctx->uploaded)
 		return SAB_ERR_STATE;
-	return (ctx->num + ctx->panel - 1) / ctx->panel;
+	return (int)ctx->panel_start.size() - 1;
 }
 
 int sab_strip_info(const sab_ctx *ctx, int32_t strip, int32_t nshards, int32_t *row0, int32_t *rows,
@@ -1539,6 +1594,7 @@ int multi_ensure(sab_multi *m, int n)
 		sab_config c = m->cfg;
 		c.device = m->ordinals[k];
 		c.shards_hint = std::max(m->want, (int)m->ordinals.size());
+		c.flags |= SAB_FLAG_INTERNAL_DYNAMIC; // strips are pulled from a shared cursor: uniform panels
 		rc[k] = sab_create(&m->ctx[k], &c);
 	};
 	if (n - have == 1) {

@@ -4,6 +4,10 @@
 
 #include <vector>
 
+// sab_config.flags bit set by sab_multi_* on its contexts (not part of the public flag set): the
+// devices pull row strips from a shared cursor, so the panels keep a uniform height (panel_bounds)
+enum { SAB_FLAG_INTERNAL_DYNAMIC = 1 << 30 };
+
 // device ordinal of the context, or -1 when it has no usable device
 int sab_internal_device(const sab_ctx *ctx);
 // records the message in the context and returns `code`

@@ -49,7 +49,7 @@ def test_golden_all_tables(flags):
 
 @pytest.mark.parametrize("method,kw", METHODS)
 @pytest.mark.parametrize("flags", [0, capi.SAB_FLAG_FORCE_INT32, capi.SAB_FLAG_STRIP16,
-                                   capi.SAB_FLAG_STRIP32,
+                                   capi.SAB_FLAG_STRIP32, capi.SAB_FLAG_SERIAL_WIDTHS,
                                    capi.SAB_FLAG_STRIP16 | capi.SAB_FLAG_FORCE_INT32])
 def test_vs_oracle_mixed_lengths(oracle_mod, method, kw, flags):
     """ragged lengths 1..420 across several panels, strips and register windows"""

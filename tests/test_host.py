@@ -115,7 +115,7 @@ def test_strip_plan_covers_rows_once_and_balances():
         rows = sorted((a, a + b) for a, b, _ in plan)
         assert rows[0][0] == 0 and rows[-1][1] == store.num
         assert all(rows[k][1] == rows[k + 1][0] for k in range(len(rows) - 1))
-        assert all(b % 128 == 0 for _, b, _ in plan[:-1])
+        assert all(b % 32 == 0 for _, b, _ in plan[:-1])
         lens = store.lengths
         pre = np.concatenate([[0], np.cumsum(lens)])
         load = np.zeros(nshards)

@@ -143,7 +143,7 @@ def main():
             csum = 0
             blk = 1 << 26
             for o in range(0, pairs, blk):
-                csum = (csum * 1000003 + int(view[o:o + blk].astype(np.int64).sum())) % (1 << 61)
+                csum = (csum * 1000003 + int(view[o:o + blk].sum(dtype=np.int64))) % (1 << 61)
             out["readback_s"] = round(time.perf_counter() - t, 3)
             out["checksum"] = csum
             if args.samples:

@@ -1,6 +1,7 @@
 #!/bin/bash
 # GPU call 2 of round 2: specialised device images (immediate gap constant), concurrent per-width launches,
-# SW row prefetch.  Full GPU test suite, A/B lines, counters of the bare DP block.
+# SW row prefetch, equal-cost row strips (auto panels; --panel N = uniform as before: 1792 / 640 were the old auto
+# choices for C2 at 1 / 8 shards).  Full GPU test suite, A/B lines, counters of the bare DP block.
 cd "$(dirname "$0")/.."
 O=gpurun_out
 mkdir -p $O
@@ -23,6 +24,8 @@ echo "pytest exit $?" >> $O/r2c2_pytest.txt
   tools/ab2.sh "default" --config c2 --emulate-shards 8 --panel 1792
   tools/ab2.sh "default" --config c2 --emulate-shards 8 --panel 1792 --flags 8
   tools/ab2.sh "default" --config c2 --emulate-shards 8 --panel 3584 --flags 8
+  tools/ab2.sh "default" --config c2 --panel 1792
+  tools/ab2.sh "default" --config c2 --emulate-shards 8 --panel 640
   tools/ab2.sh "default" --config c2 --panel 2560
   tools/ab2.sh "default" --config c2 --panel 2560 --flags 8
   tools/ab2.sh "default" --config c2 --panel 3328 --flags 8
