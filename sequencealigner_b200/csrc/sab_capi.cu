@@ -354,12 +354,12 @@ bool int16_safe(const sab_ctx *c, int lq, int ls)
 //                     sum of the lengths, so the boundaries sit where P^2 crosses k / E of its final
 //                     value: a tall strip at the top of the triangle, thin ones at the bottom, all
 //                     with the same number of cells (and, near enough, of pairs: equal buffers).
-//                     E = 2 per shard (4 for a single shard: the last strip's write-back is exposed),
-//                     more when a strip would exceed 2^29 scores (2 GiB per strip buffer).  Every
-//                     launch then has the same amount of work however many shards there are --
-//                     uniform 6-per-shard panels left the strips of an 8-GPU job at 640 rows and the
-//                     per-GPU rate 5-9 % below the 1-GPU one -- and the longest-processing-time
-//                     assignment is balanced by construction (E is a multiple of the shards).
+//                     E = 2 per shard (4 for a single shard), more when a strip would exceed 2^29
+//                     scores (2 GiB per strip buffer); the last strip of every shard is split into a
+//                     geometric tail (below).  The launches then carry the same work however many
+//                     shards there are -- uniform 6-per-shard panels left the strips of an 8-GPU job
+//                     at 640 rows and the per-GPU rate 5-9 % below the 1-GPU one -- and the longest-
+//                     processing-time assignment is balanced by construction.
 //   dynamic           (sab_multi_*: devices pull strips from a shared cursor, costliest first)
 //                     uniform height, ~6 strips per device: costs then FALL linearly along the issue
 //                     order, which is what keeps the tail of a dynamically scheduled job short.
@@ -383,14 +383,25 @@ void panel_bounds(const std::vector<int64_t> &P /* [num + 1] prefix sums of the 
 	const int64_t pairs = tri(num);
 	const int E = (int)((std::max<int64_t>(1, (pairs + (1ll << 29) - 1) >> 29) + unit - 1) / unit) * unit;
 	const int minh = 64; // two query groups
-	const double T2 = (double)P[num] * (double)P[num] / E; // cost of a strip in units of P^2 = 2 * cells
-	std::vector<int32_t> cuts; // built from the bottom of the triangle upwards
+	// Strip costs from the bottom of the triangle upwards, in units of T = total / E: E - shards
+	// full strips, then per shard a tail of T/2, T/4, T/8, T/8.  Every shard ends on small strips
+	// (the write-back of a rank's LAST strip cannot overlap with anything: for short sequences,
+	// where copying a score costs about as much as computing it, a full strip there would add
+	// 1 / strips-per-rank to the end-to-end time), and the tails sum to T per shard, so the
+	// longest-processing-time assignment still comes out even.
+	std::vector<double> frac;
+	frac.insert(frac.end(), (size_t)(E - shards), 1.0);
+	for (double f : { 0.5, 0.25, 0.125, 0.125 })
+		frac.insert(frac.end(), (size_t)shards, f);
+	const double T2 = (double)P[num] * (double)P[num] / E; // in units of P^2 = 2 * cells
+	std::vector<int32_t> cuts;
 	int a1 = num;
-	for (int k = 0; k < E - 1 && a1 > 0; k++) {
-		const double lo2 = (double)P[a1] * (double)P[a1] - T2;
+	double hi2 = (double)P[num] * (double)P[num];
+	for (size_t k = 0; k + 1 < frac.size() && a1 > 0; k++) {
+		hi2 -= frac[k] * T2; // exact targets: rounding a boundary does not shift the ones above it
 		int a0 = 0;
-		if (lo2 > 0) {
-			a0 = (int)(std::lower_bound(P.begin(), P.begin() + a1, (int64_t)std::sqrt(lo2)) - P.begin());
+		if (hi2 > 0) {
+			a0 = (int)(std::lower_bound(P.begin(), P.begin() + a1, (int64_t)std::sqrt(hi2)) - P.begin());
 			a0 = (a0 + 16) / 32 * 32;
 		}
 		a0 = std::max(0, std::min(a0, a1 - minh));

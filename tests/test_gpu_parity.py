@@ -213,6 +213,16 @@ def test_panel_size_and_sharding_do_not_change_results():
                 else:
                     assert (part[lo:hi] == -1).all()  # other shards' rows untouched
     assert np.array_equal(merged, base)
+    # auto panels = equal-cost strips + a geometric tail per shard (panel_bounds, sab_capi.cu)
+    merged = np.full_like(base, -1)
+    with Aligner(cfg, shards_hint=4) as al:
+        al.upload(store)
+        owners = al.strips(4)
+        heights = [rows for _, rows, _ in owners]
+        assert len(owners) >= 8 and len(set(heights)) > 1 and all(h % 32 == 0 for h in heights[:-1])
+        for shard in range(4):
+            al.align(out=merged, shard=shard, nshards=4)  # the shards fill disjoint rows of ONE matrix
+    assert np.array_equal(merged, base)
 
 
 @pytest.mark.parametrize("thr", [0.9, 0.5, 0.05, 1.0])
