@@ -97,7 +97,9 @@ typedef struct sab_config {
 	int32_t flags; /* enum sab_flags */
 	int32_t shards_hint; /* how many shards sab_align_shard will be called with (sizes the
 			      * auto panel so every shard gets several row strips); 0 = 1 */
-	int32_t reserved[4];
+	int32_t host_threads; /* host threads for packing the sequences and copying scores into `matrix`
+			       * (the reference's -T, src/system/os.c:466-473); 0 = min(cores, 8) */
+	int32_t reserved[3];
 } sab_config;
 
 typedef struct sab_stats {

@@ -18,6 +18,9 @@
  *
  * What crosses into the library is only the C ABI of include/seqalign_b200.h.
  */
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include "interface/seqalign_cuda.h"
 
 #include <args.h>
@@ -139,6 +142,11 @@ sab_multi *b200_context(void)
 		.gap_pen = GAP_PEN == SCORE_MIN ? 0 : GAP_PEN,
 		.gap_open = GAP_OPN == SCORE_MIN ? 0 : GAP_OPN,
 		.gap_ext = GAP_EXT == SCORE_MIN ? 0 : GAP_EXT,
+#ifdef _OPENMP
+		/* -T (os.c:466-473 has already applied it to the OpenMP runtime) also bounds the library's
+		 * host threads (sequence packing, copies into out.matrix) */
+		.host_threads = omp_get_max_threads(),
+#endif
 	};
 	if (cfg.method < 0) {
 		perr("Alignment method has no B200 kernel");

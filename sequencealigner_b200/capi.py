@@ -35,7 +35,7 @@ class SabConfig(C.Structure):
         ("method", C.c_int32), ("gap_pen", C.c_int32), ("gap_open", C.c_int32),
         ("gap_ext", C.c_int32), ("seq_lut", C.c_int32 * 128), ("sub_mat", C.c_int32 * 576),
         ("device", C.c_int32), ("panel", C.c_int32), ("flags", C.c_int32),
-        ("shards_hint", C.c_int32), ("reserved", C.c_int32 * 4),
+        ("shards_hint", C.c_int32), ("host_threads", C.c_int32), ("reserved", C.c_int32 * 3),
     ]
 
 

@@ -253,12 +253,20 @@ struct Seg {
 	size_t n;
 };
 
-// Runs fn(first, last) over [0, n) split into contiguous ranges on up to 8 host threads
-// (`work` = total units, to stay single-threaded for small inputs).
-template <typename F> void parallel_ranges(int32_t n, int64_t work, F fn)
+// Host threads a context may use for packing and for the copy into the caller's matrix:
+// sab_config.host_threads (the reference's -T), else min(cores, 8).
+int host_thread_cap(const sab_ctx *ctx)
 {
-	const unsigned hw = std::thread::hardware_concurrency();
-	const int nthreads = (int)std::min<int64_t>(std::max(1u, std::min(hw, 8u)), work / (1 << 19) + 1);
+	if (ctx && ctx->cfg.host_threads > 0)
+		return ctx->cfg.host_threads;
+	return (int)std::max(1u, std::min(std::thread::hardware_concurrency(), 8u));
+}
+
+// Runs fn(first, last) over [0, n) split into contiguous ranges on up to `cap` host threads
+// (`work` = total units, to stay single-threaded for small inputs).
+template <typename F> void parallel_ranges(int cap, int32_t n, int64_t work, F fn)
+{
+	const int nthreads = (int)std::min<int64_t>(cap, work / (1 << 19) + 1);
 	if (nthreads <= 1 || n < nthreads) {
 		fn(0, n);
 		return;
@@ -270,13 +278,12 @@ template <typename F> void parallel_ranges(int32_t n, int64_t work, F fn)
 		x.join();
 }
 
-void copy_segments(const std::vector<Seg> &segs)
+void copy_segments(int cap, const std::vector<Seg> &segs)
 {
 	size_t total = 0;
 	for (auto &s : segs)
 		total += s.n;
-	unsigned hw = std::thread::hardware_concurrency();
-	int nthreads = (int)std::min<size_t>(std::max(1u, std::min(hw, 8u)), total / (1u << 18) + 1);
+	int nthreads = (int)std::min<size_t>(cap, total / (1u << 18) + 1);
 	if (nthreads <= 1) {
 		for (auto &s : segs)
 			memcpy(s.dst, s.src, s.n * sizeof(int32_t));
@@ -756,7 +763,7 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 	std::vector<uint8_t> &col_bytes = ps.col_bytes;
 	col_bytes.assign((size_t)letters + 16, 24);
 	std::atomic<int32_t> bad_seq{ -1 };
-	parallel_ranges(num, letters, [&](int32_t s0, int32_t s1) {
+	parallel_ranges(host_thread_cap(ctx), num, letters, [&](int32_t s0, int32_t s1) {
 		for (int32_t s = s0; s < s1; s++) {
 			const uint8_t *src = seqs + meta[slot_orig[s]].off;
 			uint8_t *dst = col_bytes.data() + col_off[s];
@@ -791,7 +798,7 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 	// rows past a sequence's end hold the pad letter (24): SW sweeps them (sab_wave.cuh)
 	std::vector<uint32_t> &rowpack = ps.rowpack;
 	rowpack.assign((size_t)rows4 * 32, 0x60606060u);
-	parallel_ranges(num, letters, [&](int32_t s0, int32_t s1) { // every slot owns its own words
+	parallel_ranges(host_thread_cap(ctx), num, letters, [&](int32_t s0, int32_t s1) { // every slot owns its own words
 		for (int32_t s = s0; s < s1; s++) {
 			const uint8_t *src = col_bytes.data() + col_off[s];
 			uint32_t *dst = rowpack.data() + grp_off[s >> 5] * 32 + (s & 31);
@@ -962,7 +969,7 @@ int drain_strip(sab_ctx *ctx, const Strip &st, StripBuf &b, int32_t *matrix, int
 		if (!pending[s])
 			return SAB_OK;
 		CU(cudaEventSynchronize(ctx->ev_copy[s]));
-		copy_segments(pend_segs[s]);
+		copy_segments(host_thread_cap(ctx), pend_segs[s]);
 		pending[s] = false;
 		return SAB_OK;
 	};
@@ -1606,6 +1613,8 @@ int multi_ensure(sab_multi *m, int n)
 		c.device = m->ordinals[k];
 		c.shards_hint = std::max(m->want, (int)m->ordinals.size());
 		c.flags |= SAB_FLAG_INTERNAL_DYNAMIC; // strips are pulled from a shared cursor: uniform panels
+		if (c.host_threads > 0) // the caller's thread budget is shared by the devices
+			c.host_threads = std::max(1, c.host_threads / std::max(1, n));
 		rc[k] = sab_create(&m->ctx[k], &c);
 	};
 	if (n - have == 1) {
