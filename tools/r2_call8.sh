@@ -5,6 +5,10 @@ cd "$(dirname "$0")/.."
 O=gpurun_out
 mkdir -p $O
 { nproc; free -g; df -h /tmp /dev/shm .; nvidia-smi -L; nvidia-smi topo -m | head -12; } > $O/r2c8_box.txt 2>&1
+# one small bit-exactness check first: a broken tree must not burn 8 GPUs' worth of minutes
+if ! timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/r2c8_smoke.txt 2>&1; then
+  echo "smoke failed, stopping" >> $O/r2c8_smoke.txt; tail -5 $O/r2c8_smoke.txt; exit 1
+fi
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
 # C3: 50 000 DNA reads, SW, fixed size at every N (BASELINE.json configs[2])
 for n in 8 4 2; do
