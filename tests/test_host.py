@@ -121,7 +121,11 @@ def test_strip_plan_covers_rows_once_and_balances():
         load = np.zeros(nshards)
         for a, b, o in plan:
             load[o] += float((lens[a:a + b] * pre[a:a + b]).sum())
-        assert load.min() > 0 and load.max() / load.mean() < 1.08
+        assert load.min() > 0 and load.max() / load.mean() < 1.01
+        # every shard ends on a small strip: its last write-back is the one nothing overlaps with
+        for sh in range(nshards):
+            mine = [float((lens[a:a + b] * pre[a:a + b]).sum()) for a, b, o in plan if o == sh]
+            assert len(mine) >= 4 and min(mine) < 0.1 * sum(mine)
     assert plan_strips(store, 4) == plan_strips(store, 4)  # deterministic on every rank
 
 
