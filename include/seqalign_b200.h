@@ -81,8 +81,10 @@ enum sab_flags {
 	SAB_FLAG_TEST_RERUN_CAP = 64, /* testing: SW int16 re-run list of 4 entries (exercises the int32 re-sweep) */
 	SAB_FLAG_FILTER_SEQUENTIAL = 128, /* testing/tuning: sab_filter takes the panel-sequential path directly */
 	SAB_FLAG_TEST_FILTER_CAP = 256, /* testing: filter match list of 16 entries (exercises the fallback) */
-	SAB_FLAG_SERIAL_WIDTHS = 512, /* tuning: the per-width launches of a row strip run back to back on one stream
-				       * instead of concurrently on side streams */
+	SAB_FLAG_PER_CHUNK_WIDTHS = 1024, /* tuning: a register-strip width per subject chunk (one launch per width in
+					  * use, concurrent) instead of one width per row strip */
+	SAB_FLAG_SERIAL_WIDTHS = 512, /* tuning, with PER_CHUNK_WIDTHS: the per-width launches of a row strip run back to
+				       * back on one stream instead of concurrently on side streams */
 };
 
 typedef struct sab_config {

@@ -22,6 +22,7 @@ SAB_FLAG_TEST_RERUN_CAP = 64
 SAB_FLAG_FILTER_SEQUENTIAL = 128
 SAB_FLAG_TEST_FILTER_CAP = 256
 SAB_FLAG_SERIAL_WIDTHS = 512
+SAB_FLAG_PER_CHUNK_WIDTHS = 1024
 STATUS = {0: "SAB_OK", -1: "SAB_ERR_ARG", -2: "SAB_ERR_NODEVICE", -3: "SAB_ERR_CUDA",
           -4: "SAB_ERR_NOMEM", -5: "SAB_ERR_STATE", -6: "SAB_ERR_OVERFLOW"}
 

@@ -31,7 +31,8 @@ namespace {
 using sab::DeviceSeqs;
 using sab::TileParams;
 
-constexpr int kPanelQuantum = 128; // panels are multiples of 4 query groups
+constexpr int kPanelQuantum = 128; // explicit panel heights are multiples of 4 query groups
+constexpr double kTailBelowCellsPerPair = 12000.0; // panel_bounds: geometric tail below this mean len^2
 constexpr size_t kStageBytes = 32u << 20; // pinned bounce buffer (x2)
 constexpr unsigned kRerunCap = 1u << 20;
 constexpr int kRerunBlock = 128;
@@ -390,16 +391,22 @@ void panel_bounds(const std::vector<int64_t> &P /* [num + 1] prefix sums of the 
 	const int64_t pairs = tri(num);
 	const int E = (int)((std::max<int64_t>(1, (pairs + (1ll << 29) - 1) >> 29) + unit - 1) / unit) * unit;
 	const int minh = 64; // two query groups
-	// Strip costs from the bottom of the triangle upwards, in units of T = total / E: E - shards
-	// full strips, then per shard a tail of T/2, T/4, T/8, T/8.  Every shard ends on small strips
-	// (the write-back of a rank's LAST strip cannot overlap with anything: for short sequences,
-	// where copying a score costs about as much as computing it, a full strip there would add
-	// 1 / strips-per-rank to the end-to-end time), and the tails sum to T per shard, so the
-	// longest-processing-time assignment still comes out even.
+	// Strip costs from the bottom of the triangle upwards, in units of T = total / E.  Long
+	// sequences: E equal strips (few, large launches: 5 strips per rank instead of 2 cost 4 % of the
+	// kernel rate on C2, profiles/r2_ab_call2.txt).  Short sequences (copying a score costs about
+	// as much as computing it: C4, 4 B per 2 025 cells, D2H + host scatter = 0.9 x the kernel time):
+	// E - shards full strips, then per shard a tail of T/2, T/4, T/8, T/8 -- the write-back of a
+	// rank's LAST strip overlaps with nothing, so a rank has to end on small strips; the tails sum
+	// to T per shard and the longest-processing-time assignment still comes out even.
 	std::vector<double> frac;
-	frac.insert(frac.end(), (size_t)(E - shards), 1.0);
-	for (double f : { 0.5, 0.25, 0.125, 0.125 })
-		frac.insert(frac.end(), (size_t)shards, f);
+	const double cells_per_pair = (double)P[num] / num * ((double)P[num] / num);
+	if (cells_per_pair < kTailBelowCellsPerPair) {
+		frac.insert(frac.end(), (size_t)(E - shards), 1.0);
+		for (double f : { 0.5, 0.25, 0.125, 0.125 })
+			frac.insert(frac.end(), (size_t)shards, f);
+	} else {
+		frac.insert(frac.end(), (size_t)E, 1.0);
+	}
 	const double T2 = (double)P[num] * (double)P[num] / E; // in units of P^2 = 2 * cells
 	std::vector<int32_t> cuts;
 	int a1 = num;
@@ -411,7 +418,7 @@ void panel_bounds(const std::vector<int64_t> &P /* [num + 1] prefix sums of the 
 			a0 = (int)(std::lower_bound(P.begin(), P.begin() + a1, (int64_t)std::sqrt(hi2)) - P.begin());
 			a0 = (a0 + 16) / 32 * 32;
 		}
-		a0 = std::max(0, std::min(a0, a1 - minh));
+		a0 = std::max(0, std::min(a0, (a1 - minh) / 32 * 32)); // a1 == num need not be a multiple of 32
 		if (a0 < minh)
 			a0 = 0;
 		cuts.push_back(a0);
@@ -1073,12 +1080,16 @@ void issue_order(const sab_ctx *ctx, const std::vector<Strip> &strips, std::vect
 			 [&](int x, int y) { return strips[x].cost > strips[y].cost; });
 }
 
-// Register-strip width per subject chunk of a packed strip.  Slots are length-sorted inside a
-// panel, so the 16..128 subjects of a chunk have near-equal lengths and one width fits them all:
-// the one that minimises sum(ceil(pair length / K) * K) * column_cost(K).  Widths that only a
-// few chunks ask for are folded into the others (a launch per width has a start and a tail).
-// Out: ids = chunk indices grouped by width, first[w]..first[w+1] the group of kWidths[w].
-void choose_widths(const sab_ctx *ctx, int a1, int chunk, int nsc, std::vector<int> &ids, int *first)
+// Register-strip width of a packed strip: the one that minimises sum(ceil(pair length / K) * K) *
+// column_cost(K) over its subject pairs (C3: len 150 = 5 x 30 -> K = 30, +7 % over K = 32).
+// Under SAB_FLAG_PER_CHUNK_WIDTHS every subject chunk gets its own width instead (slots are
+// length-sorted inside a panel, so the 16..128 subjects of a chunk have near-equal lengths) and the
+// strip is launched once per width in use: measured SLOWER than one width on C2/C4/C5
+// (profiles/r2_ab_call2.txt: 8.13 against 8.87 TCUPS on C2) -- a launch per width leaves each with
+// too few work items for 592 persistent blocks, and kernels of different widths sharing an SM
+// evict each other's 64 KB of straight-line code from the instruction cache.
+// Out: ids = chunk indices grouped by width (empty: one width), first[w]..first[w+1] the group of kWidths[w].
+void choose_widths(const sab_ctx *ctx, int a1, int chunk, int nsc, bool per_chunk, std::vector<int> &ids, int *first)
 {
 	std::vector<uint8_t> best((size_t)nsc);
 	std::vector<float> cost((size_t)nsc * kNumWidths);
@@ -1099,6 +1110,23 @@ void choose_widths(const sab_ctx *ctx, int a1, int chunk, int nsc, std::vector<i
 		}
 		for (int w = 0; w < kNumWidths; w++)
 			cost[(size_t)k * kNumWidths + w] = (float)(c[w] * column_cost(kWidths[w].k));
+	}
+	if (!per_chunk) { // one width for the whole strip: the cheapest in total
+		int bw = 0;
+		double bsum = 0;
+		for (int w = 0; w < kNumWidths; w++) {
+			double sum = 0;
+			for (int k = 0; k < nsc; k++)
+				sum += cost[(size_t)k * kNumWidths + w];
+			if (w == 0 || sum < bsum) {
+				bw = w;
+				bsum = sum;
+			}
+		}
+		for (int w = 0; w <= kNumWidths; w++)
+			first[w] = w > bw ? nsc : 0;
+		ids.clear();
+		return;
 	}
 	for (int pass = 0; pass < 2; pass++) {
 		for (int w = 0; w < kNumWidths; w++)
@@ -1192,13 +1220,16 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 			for (int w = 0; w <= kNumWidths; w++)
 				first[w] = w > st.widx_fixed ? nsc : 0;
 		} else {
-			choose_widths(ctx, a1, chunk, nsc, b.chunk_host, first);
-			rc = ensure(ctx, (void **)&b.chunk_ids, &b.chunk_ids_cap, (size_t)nsc, sizeof(int));
-			if (rc)
-				return rc;
-			CU(cudaMemcpyAsync(b.chunk_ids, b.chunk_host.data(), sizeof(int) * nsc, cudaMemcpyHostToDevice,
-					   b.stream));
+			choose_widths(ctx, a1, chunk, nsc, ctx->cfg.flags & SAB_FLAG_PER_CHUNK_WIDTHS, b.chunk_host, first);
+			if (!b.chunk_host.empty()) {
+				rc = ensure(ctx, (void **)&b.chunk_ids, &b.chunk_ids_cap, (size_t)nsc, sizeof(int));
+				if (rc)
+					return rc;
+				CU(cudaMemcpyAsync(b.chunk_ids, b.chunk_host.data(), sizeof(int) * nsc, cudaMemcpyHostToDevice,
+						   b.stream));
+			}
 		}
+		const bool listed = st.widx_fixed < 0 && !b.chunk_host.empty();
 		WaveVariant var[kNumWidths];
 		int max_grid = 0;
 		for (int w = 0; w < kNumWidths; w++)
@@ -1254,7 +1285,7 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 			p.nsc = first[w + 1] - first[w];
 			if (p.nsc <= 0)
 				continue;
-			p.chunk_ids = st.widx_fixed >= 0 ? nullptr : b.chunk_ids + first[w];
+			p.chunk_ids = listed ? b.chunk_ids + first[w] : nullptr;
 			p.counter = b.counter + 4 + w; // the re-run count (counter[1]) is shared and accumulates
 			cudaStream_t s = b.stream;
 			if (li > 0 && !serial) {

@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 #ifdef SAB_PREFETCH_ROWS
 	constexpr bool kPrefetchRows = SAB_PREFETCH_ROWS;
 #else
-	constexpr bool kPrefetchRows = METHOD == M_SW;
+	constexpr bool kPrefetchRows = false;
 #endif
 	const int tid = threadIdx.x;
 	const int lane = tid & 31;
@@ -298,7 +298,8 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 		int d_s = -1, d_c0 = 0, d_l0 = 0, d_l1 = 0, d_ps = 0;
 		bool first = false, last = false;
 		uint32_t V[K], Y[K];
-		// the next row group's letters are loaded one step ahead (measured: SW +2.8 % on C3, GA +-0.5 %)
+		// experiment (-DSAB_PREFETCH_ROWS=1): the next row group's letters are loaded one step ahead.
+		// SW + 2.8 % on C3 before the gap constant became an immediate, - 1.4 % after; GA +- 0.5 %: off.
 		uint32_t wn[kGroupWords];
 		if (kPrefetchRows) {
 #pragma unroll

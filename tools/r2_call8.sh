@@ -5,9 +5,11 @@ cd "$(dirname "$0")/.."
 O=gpurun_out
 mkdir -p $O
 { nproc; free -g; df -h /tmp /dev/shm .; nvidia-smi -L; nvidia-smi topo -m | head -12; } > $O/r2c8_box.txt 2>&1
-# one small bit-exactness check first: a broken tree must not burn 8 GPUs' worth of minutes
-if ! timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/r2c8_smoke.txt 2>&1; then
-  echo "smoke failed, stopping" >> $O/r2c8_smoke.txt; tail -5 $O/r2c8_smoke.txt; exit 1
+# bit-exactness first (incl. the tests that need more than one device): a broken tree must not burn 8 GPUs' worth of minutes
+if ! timeout 600 python -m pytest tests -m gpu -x -q -p no:cacheprovider \
+     -k "multi or golden or mixed or short_sequences or file_backed or ordered or sharding or overflow or reupload or scaled or wide_ranges or filter" \
+     > $O/r2c8_pytest.txt 2>&1; then
+  echo "gpu tests failed, stopping" >> $O/r2c8_pytest.txt; tail -30 $O/r2c8_pytest.txt; exit 1
 fi
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
 # C3: 50 000 DNA reads, SW, fixed size at every N (BASELINE.json configs[2])
