@@ -34,6 +34,7 @@
 #include <thread>
 #include <vector>
 
+#include <sys/mman.h>
 #include <unistd.h>
 
 namespace {
@@ -273,7 +274,7 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 	if (!path || !seqs || !matrix || dim < 1 || compression > 9 || chunk_dim > (int)dim)
 		return SAB_ERR_ARG;
 	File F;
-	F.f = fopen(path, "wb");
+	F.f = fopen(path, "w+b"); // read/write: the uncompressed chunks are written through a shared mapping
 	if (!F.f)
 		return SAB_ERR_ARG;
 
@@ -495,9 +496,30 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 			fflush(F.f);
 			const int fd = fileno(F.f);
 			const uint64_t base = F.eof;
+			// First choice: gather straight into a shared mapping of the chunk area (the scores are
+			// written once, into the page cache); fallback: a buffer per worker + pwrite.
+			const uint64_t page = (uint64_t)sysconf(_SC_PAGESIZE);
+			const uint64_t map_off = base / page * page;
+			const size_t map_len = (size_t)(base - map_off + total * raw_bytes);
+			unsigned char *map = nullptr;
+			if (ftruncate(fd, (off_t)(base + total * raw_bytes)) == 0) {
+				void *m = mmap(nullptr, map_len, PROT_READ | PROT_WRITE, MAP_SHARED, fd, (off_t)map_off);
+				if (m != MAP_FAILED)
+					map = static_cast<unsigned char *>(m);
+			}
 			std::atomic<size_t> next{ 0 }, done{ 0 };
 			std::atomic<bool> bad{ false };
 			auto worker = [&]() {
+				if (map) {
+					for (;;) {
+						const size_t idx = next.fetch_add(1);
+						if (idx >= total)
+							break;
+						gather(idx, reinterpret_cast<int32_t *>(map + (base - map_off) + idx * raw_bytes));
+						done.fetch_add(1);
+					}
+					return;
+				}
 				int32_t *raw = new (std::nothrow) int32_t[cdim * cdim];
 				if (!raw) {
 					bad = true;
@@ -537,6 +559,8 @@ extern "C" int sab_h5_write_chunked(const char *path, const char *const *seqs, s
 			}
 			for (auto &t : th)
 				t.join();
+			if (map && munmap(map, map_len) != 0)
+				bad = true;
 			if (bad.load()) {
 				fclose(F.f);
 				return SAB_ERR_NOMEM;
