@@ -371,13 +371,14 @@ bool int16_safe(const sab_ctx *c, int lq, int ls)
 //   dynamic           (sab_multi_*: devices pull strips from a shared cursor, costliest first)
 //                     uniform height, ~6 strips per device: costs then FALL linearly along the issue
 //                     order, which is what keeps the tail of a dynamically scheduled job short.
+//                     With SAB_FLAG_ORDERED (ascending rows, file-backed sinks): equal-cost strips.
 void panel_bounds(const std::vector<int64_t> &P /* [num + 1] prefix sums of the lengths, original order */,
-		  int num, int panel, int shards_hint, bool dynamic, std::vector<int32_t> &start)
+		  int num, int panel, int shards_hint, bool dynamic, bool ordered, std::vector<int32_t> &start)
 {
 	start.clear();
 	start.push_back(0);
 	const int shards = std::max(1, shards_hint);
-	if (panel <= 0 && dynamic) {
+	if (panel <= 0 && dynamic && !ordered) {
 		panel = (num / (6 * shards) + kPanelQuantum - 1) / kPanelQuantum * kPanelQuantum;
 		panel = std::max(2 * kPanelQuantum, std::min(panel, 4096));
 	}
@@ -387,7 +388,10 @@ void panel_bounds(const std::vector<int64_t> &P /* [num + 1] prefix sums of the 
 		start.push_back(num);
 		return;
 	}
-	const int unit = shards > 1 ? 2 * shards : 4;
+	// (dynamic + SAB_FLAG_ORDERED arrives here as well: ascending issue order puts the costliest
+	// uniform panels LAST, which left the devices of the 200 000-sequence C5 run finishing up to a
+	// strip -- 30 s -- apart; equal-cost strips, 6 per device, bound that by 1 / (6 x devices))
+	const int unit = dynamic ? 6 * shards : shards > 1 ? 2 * shards : 4;
 	const int64_t pairs = tri(num);
 	const int E = (int)((std::max<int64_t>(1, (pairs + (1ll << 29) - 1) >> 29) + unit - 1) / unit) * unit;
 	const int minh = 64; // two query groups
@@ -400,7 +404,7 @@ void panel_bounds(const std::vector<int64_t> &P /* [num + 1] prefix sums of the 
 	// to T per shard and the longest-processing-time assignment still comes out even.
 	std::vector<double> frac;
 	const double cells_per_pair = (double)P[num] / num * ((double)P[num] / num);
-	if (cells_per_pair < kTailBelowCellsPerPair) {
+	if (!dynamic && cells_per_pair < kTailBelowCellsPerPair) {
 		frac.insert(frac.end(), (size_t)(E - shards), 1.0);
 		for (double f : { 0.5, 0.25, 0.125, 0.125 })
 			frac.insert(frac.end(), (size_t)shards, f);
@@ -730,7 +734,7 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 		for (int32_t k = 0; k < num; k++)
 			P[k + 1] = P[k] + meta[k].len;
 		panel_bounds(P, num, ctx->cfg.panel, ctx->cfg.shards_hint, ctx->cfg.flags & SAB_FLAG_INTERNAL_DYNAMIC,
-			     ps.panel_start);
+			     ctx->cfg.flags & SAB_FLAG_ORDERED, ps.panel_start);
 	}
 	const int npanels = (int)ps.panel_start.size() - 1;
 
@@ -1502,7 +1506,7 @@ int sab_plan_strips(const sab_meta *meta, int32_t num, int32_t panel, int32_t ns
 	for (int32_t k = 0; k < num; k++)
 		P[k + 1] = P[k] + meta[k].len;
 	std::vector<int32_t> start;
-	panel_bounds(P, num, panel, nshards, false, start);
+	panel_bounds(P, num, panel, nshards, false, false, start);
 	const int npanels = (int)start.size() - 1;
 	if (npanels > max_strips)
 		return npanels;
