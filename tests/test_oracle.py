@@ -86,3 +86,31 @@ def test_oracle_filter_matches_reference_binary(oracle_mod, tmp_path):
     assert 0 < lost.sum() < store.num
     kept = store.subset(~lost)
     assert [kept.sequence(k) for k in range(kept.num)] == ref["seqs"]
+
+
+@pytest.mark.parametrize("name,npairs", [("c5_full_200k_8gpu_samples", 1500), ("c5ovf_20k_8gpu_samples", 1200)])
+def test_full_size_gpu_run_samples_equal_the_oracle(oracle_mod, name, npairs):
+    """Scores the B200 path wrote during the FULL-SIZE runs of round 2 (C5: 200 000 sequences on 8 GPUs
+    into a file-backed sink; C5-ovf: 20 000 sequences with planted poly-W under pam500), sampled on the
+    GPU box by tools/full_run.py and committed as a fixture: a subset is re-scored here by the CPU oracle
+    (all 10^6 sampled pairs + 18 whole rows of either run were checked once by tools/verify_samples.py:
+    profiles/r2_verify_samples.json)."""
+    import numpy as np
+    from pathlib import Path
+    from sequencealigner_b200 import AlignConfig, synth
+    z = np.load(Path(__file__).parent / "golden" / f"{name}.npz")
+    n_in = int(z["sequences_in"])
+    if str(z["config"]).endswith("-ovf"):
+        store, c = synth.make_overflow(n=n_in, planted=64)
+    else:
+        store, c = synth.make(str(z["config"]), n=n_in)
+    assert store.num == int(z["n"])
+    r = AlignConfig(c["method"], c["matrix"], gap_pen=c.get("gap_pen"), gap_open=c.get("gap_open"),
+                    gap_ext=c.get("gap_ext")).resolve()
+    i, j, score = z["i"], z["j"], z["score"]
+    pick = np.argsort(-score.astype(np.int64), kind="stable")[:200]  # the highest scores (int16 overflows) ...
+    pick = np.unique(np.concatenate([pick, np.arange(npairs)]))       # ... and a prefix of the uniform sample
+    want = oracle_mod.pairs(r, store, i[pick], j[pick])
+    assert np.array_equal(want, score[pick])
+    if "ovf" in name:
+        assert score.max() == 34000  # poly-W x poly-W under pam500: beyond int16, re-scored in int32
