@@ -207,6 +207,13 @@ int sab_get_stats(const sab_ctx *ctx, sab_stats *out);
 int sab_kernel_image(int method, int packed, int width, uint32_t gap_constant, unsigned char *out,
 		     size_t cap, size_t *size, char *kernel_name, size_t name_cap);
 
+/* Host-only self-test of the upload packing: packs the set as sab_upload would (length binning, the
+ * 2-/5-bit subject bit stream, the lane-interleaved query words) and reads every letter back with the
+ * kernels' addressing.  Returns the number of letters that differ (0 = good), < 0 on errors;
+ * *bits_per_letter = subject packing chosen (2: the set uses at most four letters, else 5). */
+int sab_selftest_packing(const sab_config *cfg, const uint8_t *seqs, const sab_meta *meta, int32_t num,
+			 int32_t *bits_per_letter);
+
 /*
  * Every GPU of the box from one host process (what cuda_align needs: it is called once, on
  * the main thread, src/main.c:31): one context and one host thread per device, each device

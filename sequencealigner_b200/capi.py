@@ -80,6 +80,8 @@ SYMBOLS = {
                                   C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                   C.POINTER(C.c_int32)]),
     "sab_get_stats": (C.c_int, [C.c_void_p, C.POINTER(SabStats)]),
+    "sab_selftest_packing": (C.c_int, [C.POINTER(SabConfig), C.c_void_p, C.POINTER(SabMeta), C.c_int32,
+                                       C.POINTER(C.c_int32)]),
     "sab_kernel_image": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t,
                                    C.POINTER(C.c_size_t), C.c_char_p, C.c_size_t]),
     "sab_multi_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(SabConfig), C.c_int32]),

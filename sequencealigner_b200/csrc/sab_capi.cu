@@ -92,7 +92,9 @@ struct sab_ctx {
 	std::vector<int32_t> panel_maxlen;
 	int32_t *d_slot_len = nullptr, *d_slot_orig = nullptr;
 	int64_t *d_col_off = nullptr, *d_grp_off = nullptr;
-	uint8_t *d_col_bytes = nullptr;
+	uint32_t *d_col_words = nullptr;
+	int col_bits = 5;
+	uint32_t col_dec = 0;
 	uint32_t *d_rowpack = nullptr;
 	size_t cap_seqs[6]{}; // bytes allocated behind the six pointers above (reused across uploads)
 	// execution
@@ -218,11 +220,11 @@ void free_seqs(sab_ctx *c)
 	cudaFree(c->d_slot_orig);
 	cudaFree(c->d_col_off);
 	cudaFree(c->d_grp_off);
-	cudaFree(c->d_col_bytes);
+	cudaFree(c->d_col_words);
 	cudaFree(c->d_rowpack);
 	c->d_slot_len = c->d_slot_orig = nullptr;
 	c->d_col_off = c->d_grp_off = nullptr;
-	c->d_col_bytes = nullptr;
+	c->d_col_words = nullptr;
 	c->d_rowpack = nullptr;
 	for (size_t &cap : c->cap_seqs)
 		cap = 0;
@@ -703,7 +705,9 @@ struct PackedSet {
 	int32_t num = 0, max_len = 0;
 	std::vector<int32_t> slot_len, slot_orig, panel_maxlen, panel_start;
 	std::vector<int64_t> col_off, grp_off, len_prefix, pad16_prefix, pad32_prefix;
-	std::vector<uint8_t> col_bytes;
+	std::vector<uint32_t> col_words; // subject letters, col_bits bits each; every slot starts on a word
+	int col_bits = 5;
+	uint32_t col_dec = 0; // 2-bit code -> letter index, one byte per code
 	std::vector<uint32_t> rowpack;
 };
 
@@ -750,15 +754,12 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 		std::stable_sort(b, e, [&](int32_t x, int32_t y) { return meta[x].len < meta[y].len; });
 		ps.panel_maxlen[p] = meta[*(e - 1)].len;
 	}
-	std::vector<int64_t> &col_off = ps.col_off;
-	col_off.resize(num);
 	ps.len_prefix.resize(num + 1);
 	ps.pad16_prefix.resize(num + 1);
 	ps.pad32_prefix.resize(num + 1);
 	int64_t off = 0, off16 = 0, off32 = 0;
 	for (int32_t s = 0; s < num; s++) {
 		slot_len[s] = meta[slot_orig[s]].len;
-		col_off[s] = off;
 		ps.len_prefix[s] = off;
 		ps.pad16_prefix[s] = off16;
 		ps.pad32_prefix[s] = off32;
@@ -770,14 +771,13 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 	ps.pad16_prefix[num] = off16;
 	ps.pad32_prefix[num] = off32;
 
-	// Subject layout: one byte per residue, index 0..23.
-	std::vector<uint8_t> &col_bytes = ps.col_bytes;
-	col_bytes.assign((size_t)letters + 16, 24);
+	// Alphabet check; which of the 24 letter indices occur at all decides the packing below.
 	std::atomic<int32_t> bad_seq{ -1 };
+	std::atomic<uint32_t> used{ 0 };
 	parallel_ranges(host_thread_cap(ctx), num, letters, [&](int32_t s0, int32_t s1) {
+		uint32_t mine = 0;
 		for (int32_t s = s0; s < s1; s++) {
 			const uint8_t *src = seqs + meta[slot_orig[s]].off;
-			uint8_t *dst = col_bytes.data() + col_off[s];
 			for (int32_t k = 0; k < slot_len[s]; k++) {
 				const uint8_t ch = src[k];
 				const int32_t idx = ch < 128 ? ctx->cfg.seq_lut[ch] : -1;
@@ -785,13 +785,60 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 					bad_seq.store(slot_orig[s]);
 					return;
 				}
-				dst[k] = (uint8_t)idx;
+				mine |= 1u << idx;
 			}
 		}
+		used.fetch_or(mine);
 	});
 	if (bad_seq.load() >= 0)
 		return fail(ctx, SAB_ERR_ARG, "sequence %d has a letter outside the matrix alphabet",
 			    bad_seq.load());
+	// Subject (DP column) layout: a bit stream per slot, 2 bits per letter when the set uses at most
+	// four letters of the matrix alphabet (DNA reads: ACGT), else 5 bits (protein, IUPAC); every slot
+	// starts on a 32-bit word, so the packing threads never share a word.  Read once per strip when
+	// its profile is staged (sab_wave.cuh: build) and by the int32 re-run kernel.
+	uint8_t code_of[24] = { 0 };
+	{
+		const uint32_t u = used.load();
+		int distinct = 0;
+		for (int a = 0; a < 24; a++)
+			distinct += (u >> a) & 1;
+		ps.col_bits = distinct <= 4 ? 2 : 5;
+		ps.col_dec = 0;
+		int next = 0;
+		for (int a = 0; a < 24; a++) {
+			code_of[a] = (uint8_t)a;
+			if (ps.col_bits == 2 && ((u >> a) & 1)) {
+				code_of[a] = (uint8_t)next;
+				ps.col_dec |= (uint32_t)a << (8 * next);
+				next++;
+			}
+		}
+	}
+	const int bits = ps.col_bits;
+	std::vector<int64_t> &col_off = ps.col_off; // WORD offset of the slot in col_words
+	col_off.resize(num);
+	int64_t words = 0;
+	for (int32_t s = 0; s < num; s++) {
+		col_off[s] = words;
+		words += ((int64_t)slot_len[s] * bits + 31) / 32;
+	}
+	std::vector<uint32_t> &col_words = ps.col_words;
+	col_words.assign((size_t)words + 1, 0u);
+	parallel_ranges(host_thread_cap(ctx), num, letters, [&](int32_t s0, int32_t s1) {
+		for (int32_t s = s0; s < s1; s++) {
+			const uint8_t *src = seqs + meta[slot_orig[s]].off;
+			uint32_t *dst = col_words.data() + col_off[s];
+			for (int32_t k = 0; k < slot_len[s]; k++) {
+				const uint32_t code = code_of[ctx->cfg.seq_lut[src[k]]];
+				const int64_t b = (int64_t)k * bits;
+				const int sh = (int)(b & 31);
+				dst[b >> 5] |= code << sh;
+				if (sh + bits > 32)
+					dst[(b >> 5) + 1] |= code >> (32 - sh);
+			}
+		}
+	});
 	// Query layout: 32-slot groups, 4 residues per word (stored as byte offsets
 	// letter*4 into a profile column), lane-interleaved for coalesced loads.
 	const int ngroups = (num + 31) / 32;
@@ -811,12 +858,12 @@ int pack_set(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t nu
 	rowpack.assign((size_t)rows4 * 32, 0x60606060u);
 	parallel_ranges(host_thread_cap(ctx), num, letters, [&](int32_t s0, int32_t s1) { // every slot owns its own words
 		for (int32_t s = s0; s < s1; s++) {
-			const uint8_t *src = col_bytes.data() + col_off[s];
+			const uint8_t *src = seqs + meta[slot_orig[s]].off;
 			uint32_t *dst = rowpack.data() + grp_off[s >> 5] * 32 + (s & 31);
 			for (int32_t r = 0; r < slot_len[s]; r++) {
 				uint32_t &wd = dst[(size_t)(r >> 2) * 32];
 				const int sh = 8 * (r & 3);
-				wd = (wd & ~(0xffu << sh)) | ((uint32_t)(src[r] * 4) << sh);
+				wd = (wd & ~(0xffu << sh)) | ((uint32_t)(ctx->cfg.seq_lut[src[r]] * 4) << sh);
 			}
 		}
 	});
@@ -837,9 +884,9 @@ int install_set(sab_ctx *ctx, PackedSet &ps, bool keep)
 	// cudaFree / cudaMalloc per upload cost 0.1-0.25 s every few calls (measured): grow-only reuse
 	{
 		void **ptr[6] = { (void **)&ctx->d_slot_len, (void **)&ctx->d_slot_orig, (void **)&ctx->d_col_off,
-				  (void **)&ctx->d_grp_off, (void **)&ctx->d_col_bytes, (void **)&ctx->d_rowpack };
+				  (void **)&ctx->d_grp_off, (void **)&ctx->d_col_words, (void **)&ctx->d_rowpack };
 		const size_t need[6] = { sizeof(int32_t) * num, sizeof(int32_t) * num, sizeof(int64_t) * num,
-					 sizeof(int64_t) * ngroups, ps.col_bytes.size(),
+					 sizeof(int64_t) * ngroups, ps.col_words.size() * sizeof(uint32_t),
 					 ps.rowpack.size() * sizeof(uint32_t) };
 		for (int i = 0; i < 6; i++) {
 			const int rc = ensure(ctx, ptr[i], &ctx->cap_seqs[i], need[i], 1);
@@ -851,11 +898,13 @@ int install_set(sab_ctx *ctx, PackedSet &ps, bool keep)
 	CU(cudaMemcpy(ctx->d_slot_orig, ps.slot_orig.data(), sizeof(int32_t) * num, cudaMemcpyHostToDevice));
 	CU(cudaMemcpy(ctx->d_col_off, ps.col_off.data(), sizeof(int64_t) * num, cudaMemcpyHostToDevice));
 	CU(cudaMemcpy(ctx->d_grp_off, ps.grp_off.data(), sizeof(int64_t) * ngroups, cudaMemcpyHostToDevice));
-	CU(cudaMemcpy(ctx->d_col_bytes, ps.col_bytes.data(), ps.col_bytes.size(), cudaMemcpyHostToDevice));
+	CU(cudaMemcpy(ctx->d_col_words, ps.col_words.data(), ps.col_words.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+	ctx->col_bits = ps.col_bits;
+	ctx->col_dec = ps.col_dec;
 	CU(cudaMemcpy(ctx->d_rowpack, ps.rowpack.data(), ps.rowpack.size() * sizeof(uint32_t),
 		      cudaMemcpyHostToDevice));
 	ctx->stats.h2d_bytes = (int64_t)(sizeof(int32_t) * 2 * num + sizeof(int64_t) * (num + ngroups) +
-					 ps.col_bytes.size() + ps.rowpack.size() * sizeof(uint32_t));
+					 ps.col_words.size() * sizeof(uint32_t) + ps.rowpack.size() * sizeof(uint32_t));
 	ctx->num = num;
 	ctx->max_len = ps.max_len;
 	if (keep) {
@@ -899,6 +948,48 @@ int sab_upload(sab_ctx *ctx, const uint8_t *seqs, const sab_meta *meta, int32_t 
 		return rc;
 	ctx->stats.upload_ms = now_ms() - t0;
 	return SAB_OK;
+}
+
+// Host-only self-test of the upload packing (no device needed): packs the set as sab_upload would
+// and reads every letter back from the two device layouts with the kernels' own addressing --
+// the bit stream of the subject layout (sab_kernels.cuh: subject_letter) and the lane-interleaved
+// byte-offset words of the query layout.  Returns the number of letters that differ (0 = good),
+// < 0 on argument errors; *bits_per_letter reports the subject packing chosen (2 or 5).
+int sab_selftest_packing(const sab_config *cfg, const uint8_t *seqs, const sab_meta *meta, int32_t num,
+			 int32_t *bits_per_letter)
+{
+	if (!cfg || !seqs || !meta)
+		return SAB_ERR_ARG;
+	sab_ctx tmp;
+	tmp.cfg = *cfg;
+	tmp.gapA = cfg->method == SAB_NW ? cfg->gap_pen : cfg->gap_open;
+	tmp.gapE = cfg->method == SAB_NW ? 0 : cfg->gap_ext;
+	tmp.max_s = 1;
+	PackedSet ps;
+	const int rc = pack_set(&tmp, seqs, meta, num, 0, ps);
+	if (rc)
+		return rc;
+	if (bits_per_letter)
+		*bits_per_letter = ps.col_bits;
+	int64_t bad = 0;
+	for (int32_t s = 0; s < num; s++) {
+		const uint8_t *src = seqs + meta[ps.slot_orig[s]].off;
+		const uint32_t *w = ps.col_words.data() + ps.col_off[s];
+		const uint32_t *rp = ps.rowpack.data() + ps.grp_off[s >> 5] * 32 + (s & 31);
+		if (ps.slot_len[s] != meta[ps.slot_orig[s]].len)
+			bad++;
+		for (int32_t k = 0; k < ps.slot_len[s]; k++) {
+			const int want = cfg->seq_lut[src[k]];
+			const int b = k * ps.col_bits, sh = b & 31;
+			uint32_t v = w[b >> 5] >> sh;
+			if (sh + ps.col_bits > 32)
+				v |= w[(b >> 5) + 1] << (32 - sh);
+			const int got = ps.col_bits == 2 ? (int)((ps.col_dec >> (8 * (v & 3u))) & 0xffu) : (int)(v & 31u);
+			const int rowgot = (int)((rp[(size_t)(k >> 2) * 32] >> (8 * (k & 3))) & 0xffu) / 4;
+			bad += (got != want) + (rowgot != want);
+		}
+	}
+	return (int)std::min<int64_t>(bad, INT32_MAX);
 }
 
 // Strip bookkeeping ------------------------------------------------------------------------
@@ -1182,8 +1273,8 @@ int align_strips(sab_ctx *ctx, const std::vector<Strip> &strips, StripSource &sr
 	S.filter_ms = flt_ms;
 	S.filter_matches = flt_m;
 
-	DeviceSeqs dseqs{ ctx->d_slot_len, ctx->d_slot_orig, ctx->d_col_off, ctx->d_col_bytes,
-			  ctx->d_grp_off, ctx->d_rowpack };
+	DeviceSeqs dseqs{ ctx->d_slot_len, ctx->d_slot_orig, ctx->d_col_off, ctx->d_col_words,
+			  ctx->d_grp_off, ctx->d_rowpack,   ctx->col_bits,   ctx->col_dec };
 	const int bnd_rows = (ctx->max_len + 8 + 3) / 4 * 4;
 	int64_t pairs_done = 0;
 	std::vector<std::pair<float, float>> spans; // kernel intervals on the device timeline

@@ -49,11 +49,27 @@ __host__ __device__ inline int profile_shift(int method, int gapA, int gapE)
 struct DeviceSeqs {
 	const int32_t *slot_len; // [nslots]   length of the sequence in slot s
 	const int32_t *slot_orig; // [nslots]   original index of the sequence in slot s
-	const int64_t *col_off; // [nslots]   byte offset of the slot's letters in col_bytes
-	const uint8_t *col_bytes; // letter indices 0..23, one byte per residue
+	const int64_t *col_off; // [nslots]   word offset of the slot's letters in col_words
+	const uint32_t *col_words; // subject letters as a bit stream per slot, col_bits bits per letter
 	const int64_t *grp_off; // [ngroups]  row4 offset of the 32-slot group in rowpack
 	const uint32_t *rowpack; // [(grp_off[g] + r/4) * 32 + lane] = 4 letters * 4 (byte offsets)
+	int col_bits; // 2: the set uses <= 4 letters of the alphabet (ACGT reads), codes via col_dec; 5: letter index
+	uint32_t col_dec; // 2-bit code -> letter index, one byte per code
 };
+
+// Letter index (0..23) of residue `pos` of the sequence in `slot`.
+__device__ __forceinline__ int subject_letter(const DeviceSeqs &q, const int slot, const int pos)
+{
+	const uint32_t *w = q.col_words + q.col_off[slot];
+	const int b = pos * q.col_bits;
+	const int sh = b & 31;
+	uint32_t v = w[b >> 5] >> sh;
+	if (sh + q.col_bits > 32) // a 5-bit letter may straddle two words (of the same slot)
+		v |= w[(b >> 5) + 1] << (32 - sh);
+	if (q.col_bits == 2)
+		return (int)((q.col_dec >> (8 * (v & 3u))) & 0xffu);
+	return (int)(v & 31u);
+}
 
 // One launch = one ROW STRIP of the score matrix: the queries are the slots of panel
 // `a` (original indices [a_orig0, a_orig0 + a_n)), the subjects every slot below them.
@@ -207,18 +223,16 @@ __global__ void sab_rerun_sw_kernel(const RerunParams p)
 		const unsigned long long ent = p.list[k];
 		const int t = (int)(ent >> 32), s = (int)(ent & 0xffffffffu);
 		const int Lq = p.seqs.slot_len[t], Ls = p.seqs.slot_len[s];
-		const uint8_t *qs = p.seqs.col_bytes + p.seqs.col_off[t];
-		const uint8_t *ss = p.seqs.col_bytes + p.seqs.col_off[s];
 		for (int c = 0; c <= Ls; c++) {
 			m[c * st] = 0;
 			y[c * st] = NEG;
 		}
 		int best = 0;
 		for (int r = 0; r < Lq; r++) {
-			const int32_t *srow = p.sub25 + qs[r] * kLetters;
+			const int32_t *srow = p.sub25 + subject_letter(p.seqs, t, r) * kLetters;
 			int diag = m[0], left = 0, x = NEG;
 			for (int c = 1; c <= Ls; c++) {
-				const int sub = srow[ss[c - 1]] + o; // sub25 carries -gapA
+				const int sub = srow[subject_letter(p.seqs, s, c - 1)] + o; // sub25 carries -gapA
 				const int d = diag + sub;
 				const int up = m[c * st];
 				x = max(left + o, x + e);

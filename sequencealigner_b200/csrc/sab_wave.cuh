@@ -275,9 +275,9 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 			if (my_s >= 0) {
 				const int c = my_c0 + lane;
 				if (c < my_l0)
-					a0 = p.seqs.col_bytes[p.seqs.col_off[my_s] + c];
+					a0 = subject_letter(p.seqs, my_s, c);
 				if (PACKED && c < my_l1)
-					a1 = p.seqs.col_bytes[p.seqs.col_off[my_s + 1] + c];
+					a1 = subject_letter(p.seqs, my_s + 1, c);
 			}
 			if (K == 32 || lane < K) { // lane = column of the strip
 				uint32_t *dst = sm.prof[pb][warp][lane < K ? lane : 0];

@@ -217,3 +217,24 @@ def test_kernel_images_are_specialised_by_immediate_only(tmp_path, method, packe
     # every other kernel of the image still carries its placeholder (they are specialised separately)
     assert sum(x != y for x, y in zip(raw0, raw1)) <= 4 * sites1
     assert lib.sab_kernel_image(method, 0, 24, value, None, 0, C.byref(size), name, 200) < 0
+
+
+@pytest.mark.parametrize("config,n,bits", [("c3", 700, 2), ("c2", 300, 5), ("c5", 500, 5), ("c4", 900, 5)])
+def test_upload_packing_roundtrip(config, n, bits):
+    """sab_upload's device layouts read back on the host with the kernels' addressing: the subject bit
+    stream (2 bits per letter for ACGT reads, 5 for protein; a 5-bit letter may straddle two words) and
+    the lane-interleaved query words, for every letter of every sequence (no device needed)."""
+    store, c = synth.make(config, n=n)
+    cfg = AlignConfig(c["method"], c["matrix"], gap_pen=c.get("gap_pen"), gap_open=c.get("gap_open"),
+                      gap_ext=c.get("gap_ext"))
+    lib = capi.load()
+    r = cfg.resolve()
+    sc = capi.SabConfig()
+    sc.method = int(r["method"])
+    sc.gap_pen, sc.gap_open, sc.gap_ext = int(r["gap_pen"]), int(r["gap_open"]), int(r["gap_ext"])
+    sc.seq_lut[:] = [int(v) for v in np.asarray(r["seq_lut"]).reshape(128)]
+    sc.sub_mat[:] = [int(v) for v in np.asarray(r["sub_mat"]).reshape(576)]
+    got = C.c_int32(0)
+    meta = store.meta.ctypes.data_as(C.POINTER(capi.SabMeta))
+    bad = lib.sab_selftest_packing(C.byref(sc), store.seqs.ctypes.data, meta, store.num, C.byref(got))
+    assert bad == 0 and got.value == bits

@@ -98,7 +98,7 @@ def test_full_size_gpu_run_samples_equal_the_oracle(oracle_mod, name, npairs):
     import numpy as np
     from pathlib import Path
     from sequencealigner_b200 import AlignConfig, synth
-    z = np.load(Path(__file__).parent / "golden" / f"{name}.npz")
+    z = np.load(Path(__file__).parent / "golden" / "gpu_samples" / f"{name}.npz")
     n_in = int(z["sequences_in"])
     if str(z["config"]).endswith("-ovf"):
         store, c = synth.make_overflow(n=n_in, planted=64)
