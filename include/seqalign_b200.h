@@ -124,8 +124,8 @@ typedef struct sab_stats {
 	int64_t filter_matches; /* pairs that passed the threshold in the last sab_filter* (-1: sequential path) */
 	double filter_ms; /* wall time of the last sab_filter* / sab_multi_filter */
 	int32_t width_launches[16]; /* kernel launches per register-strip width, widest (32) first in steps of
-				     * 2 columns down to 16: a strip is launched once per width its subject
-				     * chunks prefer */
+				     * 2 columns down to 16: a row strip runs at the width that pads its
+				     * subjects least (under SAB_FLAG_PER_CHUNK_WIDTHS: once per width in use) */
 } sab_stats;
 
 typedef struct sab_ctx sab_ctx;

@@ -155,10 +155,10 @@ int ensure(sab_ctx *ctx, void **p, size_t *cap, size_t need, size_t elem)
 	return SAB_OK;
 }
 
-// Register-strip widths (DP columns a warp holds in registers).  The kernel is instantiated once
-// per width (sab_wave_inst.cu); a row strip is launched once per width that some of its subject
-// chunks prefer (choose_widths), so subjects pad to the next multiple of THEIR best width instead
-// of a global 32 or 16.  Widest first; int32 strips use the first and the last entry only.
+// Register-strip widths (DP columns a warp holds in registers).  The kernel exists once per width
+// (one device image each, sab_wave_inst.cu / sab_module.cu); a row strip runs at the width that pads
+// its subjects least (choose_widths) instead of a global 32 or 16.  Widest first; int32 strips use
+// the first and the last entry only.
 struct WidthInfo {
 	int k;
 	int smem; // sizeof(WaveSmem<K>)
@@ -1002,7 +1002,7 @@ struct Strip {
 	double cost; // sum len_q * sum len_s (approx. cells)
 	bool packed;
 	int widx_fixed; // index into kWidths when the whole strip runs at one width (int32 strips, the
-			// STRIP32/STRIP16 flags), -1 = per subject chunk (choose_widths)
+			// STRIP32/STRIP16 flags), -1 = chosen at launch time (choose_widths)
 	int lq, ls; // longest query / subject
 	double mean_ls; // mean subject length (strip width and chunk size heuristics)
 };
@@ -1029,7 +1029,7 @@ void plan_strips(const sab_ctx *ctx, int nshards, std::vector<Strip> &strips, st
 		const double ls_sum = (double)ctx->len_prefix[s.a0] + 0.5 * lq_sum;
 		s.cost = lq_sum * ls_sum;
 		s.packed = !force32 && (force16 || int16_safe(ctx, s.lq, s.ls));
-		// Strip width: packed strips choose it per subject chunk at launch time (choose_widths).
+		// Strip width: packed strips choose it at launch time (choose_widths).
 		// int32 strips exist at the widest and the narrowest width only: the subjects of the strip
 		// (every slot below its last query) padded to 16 or to 32 DP columns, weighted by what a
 		// column costs at either width.

@@ -141,8 +141,8 @@ template <int K> __device__ __forceinline__ uint32_t pick_column(const uint32_t 
 }
 #endif
 
-// K = DP columns a warp holds in registers (strip width): 16..32 in steps of 2, chosen per subject
-// chunk by the host (sab_capi.cu: choose_widths); narrow strips fit 5 resident blocks per SM.
+// K = DP columns a warp holds in registers (strip width): 16..32 in steps of 2, chosen per row
+// strip by the host (sab_capi.cu: choose_widths); narrow strips fit 5 resident blocks per SM.
 template <int METHOD, bool PACKED, int K, int MINB>
 __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const TileParams p)
 {
