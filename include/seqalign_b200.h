@@ -28,6 +28,9 @@
  *        <- parse_matrix                     src/bio/matrices.c:44-57
  *   sab_h5_write
  *        <- flush_hdf5                       src/io/format/hdf5.c:14-202
+ *   sab_source_format / sab_parse_fasta / sab_dsv_header / sab_parse_dsv / sab_build_meta
+ *        <- parse_fasta, parse_dsv           src/io/source/fasta.c:16-85, src/io/source/dsv.c:80-230
+ *           and the meta pass of input_load  src/io/input.c:70-81
  *
  * The reference-signature shim on top of this ABI (`bool cuda_align(struct input,
  * struct output)`, `bool cuda_memory(size_t)`, src/interface/seqalign_cuda.h:7-9)
@@ -47,7 +50,7 @@
 extern "C" {
 #endif
 
-#define SAB_ABI_VERSION 2
+#define SAB_ABI_VERSION 3
 
 enum sab_status {
 	SAB_OK = 0,
@@ -59,6 +62,8 @@ enum sab_status {
 	SAB_ERR_OVERFLOW = -6, /* sab_filter_matches only: more matching pairs than the caller's list holds
 				* (the alignment path never returns it: an SW strip whose int16 re-run
 				* list runs full is swept again in int32) */
+	SAB_ERR_PARSE = -7, /* sab_parse_* / sab_dsv_header: the input text is rejected; `err` holds the
+			     * reference's own message for it (e.g. "Sequence #3 is invalid") */
 };
 
 /* src/bio/method/{nw,ga,sw}.c */
@@ -286,6 +291,49 @@ int sab_h5_write_chunked(const char *path, const char *const *seqs, size_t dim, 
 			 sab_h5_progress_fn progress, void *user);
 /* Chunk edge the reference's rule evaluates to (hdf5.c:68-84); 0 = contiguous. */
 int sab_h5_chunk_dim(size_t dim);
+
+/*
+ * Input formats before the path (host only, no device needed): the text parsers that build the
+ * sequence store sab_upload takes.  Same accept/reject decisions, same store and the same
+ * messages as the reference's parsers; one pass, table driven, in place.
+ *
+ * `file` holds the whole input file (`bytes` of it) and is rewritten IN PLACE, front to back,
+ * into the store layout of struct input (src/io/input.h:6-11): upper-cased letters, blanks,
+ * line ends (and, DSV, quotes) dropped, one NUL after every sequence.  The store never outgrows
+ * the text it came from, with one exception the reference shares: a headerless single-column
+ * DSV file whose last row has no line end needs file[bytes] for the final NUL.
+ * seq_lut = SEQ_LUT of the selected matrix (every stored letter has seq_lut[c] >= 0); gap_pen =
+ * GAP_PEN (<= 0), which bounds the sequence length (sequence_length_limit, src/io/input.c:15-19).
+ * On SAB_ERR_PARSE `err` (capacity err_cap, may be NULL) receives the message the reference
+ * prints for that input and the content of `file` is unspecified.
+ */
+enum sab_source { SAB_SRC_NONE = 0, SAB_SRC_FASTA = 1, SAB_SRC_DSV = 2 };
+/* Format of a file by its extension (case-insensitive, without the dot): fasta fa fas fna ffn faa
+ * frn mpfa (src/io/source/fasta.c:12-14); csv ',' tsv '\t' ssv ';' psv '|' (src/io/source/dsv.c:14-19,
+ * *delimiter receives the field separator).  SAB_SRC_NONE: no parser takes it. */
+int sab_source_format(const char *ext, uint8_t *delimiter);
+/* parse_fasta, src/io/source/fasta.c:26-85: a record = header line ('>' up to the first line end)
+ * + letters up to the next '>'.  *num = records, *max = longest sequence. */
+int sab_parse_fasta(uint8_t *file, size_t bytes, const int32_t seq_lut[128], int32_t gap_pen,
+		    int32_t *num, int32_t *max, char *err, size_t err_cap);
+/* First row of a DSV file (src/io/source/dsv.c:94-144): *columns = fields of the row, *seq_column =
+ * the first one named sequence / seq / protein / dna / rna / amino / peptide / chain (any case), or
+ * -1 -- the reference then ASKS which column holds the sequences and whether the first row is a
+ * header at all (dsv.c:146-160); the host does the asking and passes the answer to sab_parse_dsv.
+ * `names` (may be NULL) receives the field texts, each NUL-terminated, back to back.
+ * SAB_ERR_PARSE "First row has empty column" as dsv.c:106-112. */
+int sab_dsv_header(const uint8_t *file, size_t bytes, uint8_t delimiter, int32_t *columns,
+		   int32_t *seq_column, char *names, size_t names_cap, char *err, size_t err_cap);
+/* The row loop of parse_dsv (src/io/source/dsv.c:163-227): field `seq_column` of every row is a
+ * sequence; quoting as dsv_field (dsv.c:26-57: a delimiter or line end inside "..." belongs to the
+ * field, "" is a quote); rows with fewer or more than the first row's columns are errors.
+ * first_row_is_data != 0: there is no header row (the reference's "No header line" answer). */
+int sab_parse_dsv(uint8_t *file, size_t bytes, uint8_t delimiter, int32_t seq_column,
+		  int first_row_is_data, const int32_t seq_lut[128], int32_t gap_pen, int32_t *num,
+		  int32_t *max, char *err, size_t err_cap);
+/* meta[k] = (offset, length) of the k-th NUL-terminated sequence of a store written by
+ * sab_parse_* (src/io/input.c:70-81).  Returns the store's size in bytes (terminators included). */
+int64_t sab_build_meta(const uint8_t *seqs, int32_t num, sab_meta *meta);
 
 #ifdef __cplusplus
 }

@@ -196,3 +196,43 @@ def run_reference(fasta_path, cli_args, threads: int = 0, write: bool = True, be
             if m:
                 res["align_seconds"] = float(m.group(1))
         return res
+
+
+def reference_parse(data: bytes, ext: str, matrix: str = "blosum62", gap_pen: int = 1,
+                    column: int | None = None, header: bool = True, binary: Path | None = None,
+                    extra_args=(), read_sequences=None):
+    """What the reference's input_load makes of a file (src/io/input.c:28-81 with the parsers
+    src/io/source/{fasta,dsv}.c): runs a `seqalign` binary on it and returns
+    dict(seqs=[...] | None, error=<the perr line> | None, choices=<entries of the column prompt>).
+    A DSV file without a recognised header name makes the reference ASK (dsv.c:146-160); the
+    answers are `column` (zero-based) and `header` (False = its "No header line" entry).
+    `binary` / `extra_args` / `read_sequences(path)`: the same run with another build of the CLI
+    (the drop-in, whose output file is HDF5)."""
+    binary = Path(binary or ref_binary())
+    with tempfile.TemporaryDirectory() as td:
+        src = Path(td) / f"in.{ext}"
+        src.write_bytes(data)
+        out = Path(td) / "out.bin"
+        cmd = [str(binary), "-i", str(src), "-o", str(out), "-m", matrix, "-a", "nw", "-p",
+               str(gap_pen), "-T", "1", "-Q", "-P", "-F", *extra_args]
+        e = {k: v for k, v in os.environ.items() if not k.startswith(("OMP_", "GOMP_", "KMP_"))}
+
+        def run(answers):
+            # the prompt re-asks forever at end of input: pad with an always-valid answer
+            feed = "".join(f"{a}\n" for a in answers) + "1\n" * 8
+            return subprocess.run(cmd, input=feed, capture_output=True, text=True, env=e, timeout=60,
+                                  errors="replace")
+        p = run([])
+        choices = None
+        m = re.search(r"Enter column number \(1-(\d+)\)", p.stdout)
+        if m:  # it asked: run again with the caller's answers
+            choices = int(m.group(1))
+            if out.exists():
+                out.unlink()
+            col = 0 if column is None else column
+            p = run([col + 1] if header else [choices, col + 1])
+        if p.returncode == 0:
+            seqs = read_sequences(out) if read_sequences else read_raw_dump(out)[2]
+            return dict(seqs=seqs, error=None, choices=choices)
+        lines = [l.strip() for l in p.stderr.splitlines() if l.strip()]
+        return dict(seqs=None, error=lines[0] if lines else f"exit {p.returncode}", choices=choices)

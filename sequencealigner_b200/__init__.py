@@ -4,7 +4,7 @@ jakovdev/SequenceAligner.  The product is libseqalign_b200.so (C ABI:
 include/seqalign_b200.h); this package is the Python host binding around it."""
 from .aligner import (AlignConfig, Aligner, MultiAligner, align_all, matrix_lookup,  # noqa: F401
                       matrix_names)
-from .seqstore import SeqStore, read_fasta  # noqa: F401
+from .seqstore import ParseError, SeqStore, parse_source, read_fasta, read_source  # noqa: F401
 
 __all__ = ["AlignConfig", "Aligner", "MultiAligner", "align_all", "matrix_lookup", "matrix_names", "SeqStore",
-           "read_fasta"]
+           "ParseError", "parse_source", "read_fasta", "read_source"]

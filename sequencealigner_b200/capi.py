@@ -12,6 +12,8 @@ from pathlib import Path
 from .build import LIB
 
 SAB_OK = 0
+SAB_ERR_PARSE = -7
+SAB_SRC_NONE, SAB_SRC_FASTA, SAB_SRC_DSV = 0, 1, 2
 SAB_NW, SAB_GA, SAB_SW = 0, 1, 2
 SAB_FLAG_FORCE_INT32 = 1
 SAB_FLAG_FORCE_INT16 = 2
@@ -24,7 +26,7 @@ SAB_FLAG_TEST_FILTER_CAP = 256
 SAB_FLAG_SERIAL_WIDTHS = 512
 SAB_FLAG_PER_CHUNK_WIDTHS = 1024
 STATUS = {0: "SAB_OK", -1: "SAB_ERR_ARG", -2: "SAB_ERR_NODEVICE", -3: "SAB_ERR_CUDA",
-          -4: "SAB_ERR_NOMEM", -5: "SAB_ERR_STATE", -6: "SAB_ERR_OVERFLOW"}
+          -4: "SAB_ERR_NOMEM", -5: "SAB_ERR_STATE", -6: "SAB_ERR_OVERFLOW", -7: "SAB_ERR_PARSE"}
 
 
 class SabMeta(C.Structure):
@@ -107,6 +109,15 @@ SYMBOLS = {
     "sab_h5_write_chunked": (C.c_int, [C.c_char_p, C.POINTER(C.c_char_p), C.c_size_t, C.c_void_p,
                                        C.c_int, C.c_uint, C.c_int, C.c_void_p, C.c_void_p]),
     "sab_h5_chunk_dim": (C.c_int, [C.c_size_t]),
+    "sab_source_format": (C.c_int, [C.c_char_p, C.POINTER(C.c_uint8)]),
+    "sab_parse_fasta": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_int32), C.c_int32,
+                                  C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_char_p, C.c_size_t]),
+    "sab_dsv_header": (C.c_int, [C.c_void_p, C.c_size_t, C.c_uint8, C.POINTER(C.c_int32),
+                                 C.POINTER(C.c_int32), C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]),
+    "sab_parse_dsv": (C.c_int, [C.c_void_p, C.c_size_t, C.c_uint8, C.c_int32, C.c_int,
+                                C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_int32),
+                                C.POINTER(C.c_int32), C.c_char_p, C.c_size_t]),
+    "sab_build_meta": (C.c_int64, [C.c_void_p, C.c_int32, C.POINTER(SabMeta)]),
 }
 
 _lib = None
@@ -127,7 +138,7 @@ def load(path: Path | None = None) -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export it
         fn.restype = res
         fn.argtypes = args
-    if lib.sab_abi_version() != 2:
+    if lib.sab_abi_version() != 3:
         raise RuntimeError("libseqalign_b200.so ABI version mismatch")
     if path is None:
         _lib = lib

@@ -3,9 +3,10 @@
 Mirrors `struct input {uchar *seqs; struct meta *meta; s32 max; s32 num;}`
 (reference: src/io/input.h:6-11, src/bio/align.h:6-9): uppercase ASCII letters,
 every sequence NUL-terminated, back to back in one buffer; meta[k] = (off, len).
-Parsing follows the reference's FASTA reader (src/io/source/fasta.c:16-85):
-letters are upper-cased, blanks and line ends skipped, every letter must be in
-the selected matrix's alphabet, empty sequences are errors.
+Files are parsed by the library (sab_parse_fasta / sab_parse_dsv, csrc/sab_source.cpp), which
+restates the reference's readers (src/io/source/fasta.c:16-85, src/io/source/dsv.c:80-230):
+letters are upper-cased, blanks and line ends skipped, every letter must be in the selected
+matrix's alphabet, empty sequences are errors -- with the reference's own message.
 """
 from __future__ import annotations
 
@@ -105,23 +106,78 @@ class SeqStore:
                 f.write(b"\n")
 
 
-def read_fasta(path, seq_lut=None) -> SeqStore:
-    """fasta.c:16-85 semantics.  `seq_lut` (int32[128]) validates the alphabet."""
-    data = open(path, "rb").read()
-    if not data.startswith(b">"):
-        raise ValueError("Data before first header")
-    out = []
-    for rec in data.split(b">")[1:]:
-        nl = rec.find(b"\n")
-        if nl < 0:
-            raise ValueError("Last header has no data")
-        body = rec[nl + 1:].upper().translate(None, b"\r\n ")
-        if not body:
-            raise ValueError(f"Sequence #{len(out) + 1} is empty")
-        arr = np.frombuffer(body, dtype=np.uint8)
-        if arr.max() > 127 or arr.min() == 0:
-            raise ValueError(f"Sequence #{len(out) + 1} is corrupted")
-        if seq_lut is not None and (np.asarray(seq_lut)[arr] < 0).any():
-            raise ValueError(f"Sequence #{len(out) + 1} is invalid")
-        out.append(body)
-    return SeqStore.from_sequences(out)
+class ParseError(ValueError):
+    """The input text was rejected; the message is the reference's own (perr line)."""
+
+
+def parse_source(data: bytes, ext: str, seq_lut, gap_pen: int = 0, column: int | None = None,
+                 header: bool = True) -> SeqStore:
+    """The reference's input_load (src/io/input.c:28-81) on an in-memory file: picks the parser by
+    extension, runs it (libseqalign_b200.so: sab_parse_fasta / sab_parse_dsv, which restate
+    src/io/source/fasta.c:16-85 and src/io/source/dsv.c:80-230) and builds the meta table.
+
+    `seq_lut` = SEQ_LUT of the selected matrix, `gap_pen` <= 0 = GAP_PEN (bounds the lengths).
+    DSV: the sequence column is found by its header name (sequence, seq, protein, ...); where the
+    reference would ASK (no such name, dsv.c:146-160) the caller answers through `column`
+    (zero-based) and `header` (False = the first row is data, the "No header line" answer)."""
+    import ctypes as C
+
+    from . import capi
+    lib = capi.load()
+    lut = (C.c_int32 * 128)(*[int(v) for v in np.asarray(seq_lut).reshape(128)])
+    delim = C.c_uint8(0)
+    kind = lib.sab_source_format(ext.encode(), C.byref(delim))
+    if kind == capi.SAB_SRC_NONE:
+        raise ParseError(f"Unsupported file format: .{ext}")
+    buf = np.zeros(len(data) + 1, dtype=np.uint8)  # + 1: see the header's note on headerless DSV
+    buf[:len(data)] = np.frombuffer(data, dtype=np.uint8)
+    num, longest = C.c_int32(0), C.c_int32(0)
+    err = C.create_string_buffer(256)
+    if kind == capi.SAB_SRC_FASTA:
+        rc = lib.sab_parse_fasta(buf.ctypes.data, len(data), lut, gap_pen, C.byref(num),
+                                 C.byref(longest), err, len(err))
+    else:
+        cols, found = C.c_int32(0), C.c_int32(-1)
+        names = C.create_string_buffer(len(data) + 1)
+        rc = lib.sab_dsv_header(buf.ctypes.data, len(data), delim, C.byref(cols), C.byref(found),
+                                names, len(names), err, len(err))
+        if rc == capi.SAB_OK:
+            if column is None:
+                if found.value < 0:
+                    shown = names.raw.split(b"\0")[:cols.value]
+                    raise ParseError("no column is named like a sequence column; pass column= "
+                                     f"(and header=False if the first row is data): {shown}")
+                column = found.value
+            if not 0 <= column < cols.value:
+                raise ParseError(f"column {column} out of range (the first row has {cols.value})")
+            rc = lib.sab_parse_dsv(buf.ctypes.data, len(data), delim, column, int(not header), lut,
+                                   gap_pen, C.byref(num), C.byref(longest), err, len(err))
+    if rc == capi.SAB_ERR_PARSE:
+        raise ParseError(err.value.decode())
+    if rc != capi.SAB_OK:
+        raise capi.SabError(rc, "input rejected (too large, or gap_pen > 0)")
+    if num.value < 2:  # SEQ_N_MIN, src/io/input.c:64-67
+        raise ParseError(f"Not enough sequences: {num.value} (min: 2)")
+    meta = np.zeros(num.value, dtype=META_DTYPE)
+    size = lib.sab_build_meta(buf.ctypes.data, num.value, meta.ctypes.data_as(C.POINTER(capi.SabMeta)))
+    store = SeqStore(buf[:size].copy(), meta)
+    assert store.max == longest.value
+    return store
+
+
+def read_source(path, seq_lut, gap_pen: int = 0, column: int | None = None,
+                header: bool = True) -> SeqStore:
+    """input_load for a file on disk: the extension after the last dot selects the parser
+    (src/io/input.c:31-36)."""
+    from pathlib import Path
+    name = Path(path).name
+    dot = name.rfind(".")
+    if dot <= 0:
+        raise ParseError(f"File extension not found: {name}")
+    return parse_source(Path(path).read_bytes(), name[dot + 1:], seq_lut, gap_pen, column, header)
+
+
+def read_fasta(path, seq_lut) -> SeqStore:
+    """fasta.c:16-85 on a file of any name."""
+    from pathlib import Path
+    return parse_source(Path(path).read_bytes(), "fasta", seq_lut)

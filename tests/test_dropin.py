@@ -99,6 +99,35 @@ def test_dropin_cli_and_hdf5_writer_on_the_reference_cpu_path(name):
     assert np.array_equal(mat, golden_full(g))
 
 
+def test_dropin_parsers_on_the_reference_parser_goldens(oracle_mod):
+    """No GPU needed (-C): the drop-in's FASTA / DSV plugins (integration/source_b200.c on
+    sab_parse_fasta / sab_parse_dsv), prompts included, against what the reference's own
+    src/io/source/{fasta,dsv}.c made of the same files (tests/golden/sources.json)."""
+    import base64
+    import json
+    import h5min
+    ensure_built()
+    cases = json.loads((ROOT / "tests" / "golden" / "sources.json").read_text())["cases"]
+    assert len(cases) > 250
+    for c in cases:
+        o = c["options"]
+        r = oracle_mod.reference_parse(base64.b64decode(c["data"]), c["ext"], matrix=o.get("matrix", "blosum62"),
+                                       gap_pen=o.get("gap_pen", 1), column=o.get("column"),
+                                       header=o.get("header", True), binary=BIN, extra_args=["-C"],
+                                       read_sequences=lambda f: h5min.read_similarity_file(f)[0])
+        want = c["expect"]
+        assert (r["choices"] is not None) == want["asked"], (c["name"], r)
+        if "seqs" in want:
+            assert r["seqs"] == [s.encode("latin-1") for s in want["seqs"]], (c["name"], r, want)
+        else:
+            assert r["error"] == want["error"], (c["name"], r, want)
+    # the one-column file answered "No header line", which the reference cannot get past (its second
+    # prompt is refused, tests/test_sources.py): read as that column
+    r = oracle_mod.reference_parse(b"ACD\nWWY\nKLM", "csv", column=0, header=False, binary=BIN, extra_args=["-C"],
+                                   read_sequences=lambda f: h5min.read_similarity_file(f)[0])
+    assert r["seqs"] == [b"ACD", b"WWY", b"KLM"] and r["choices"] == 2
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", golden_cases())
 def test_dropin_matches_reference_cpu_build(name):

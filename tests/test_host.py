@@ -20,7 +20,7 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), name
     assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
-    assert capi.load().sab_abi_version() == 2
+    assert capi.load().sab_abi_version() == 3
 
 
 def test_struct_sizes_match_header():
