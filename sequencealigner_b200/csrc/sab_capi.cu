@@ -200,13 +200,17 @@ int wave_variant(sab_ctx *ctx, int method, bool packed, int widx, WaveVariant *o
 		int occ = 0;
 		void *fn = nullptr;
 		std::string err;
+		// cbnd, the last member of WaveSmem, belongs to the hoisted boundary exchange (sab_wave.cuh):
+		// methods built without it (SW) do not get the 2 KB
+		const int smem = kWidths[widx].smem -
+				 (SAB_HOIST_METHODS(method) ? 0 : (int)sizeof(sab::WaveSmem<sab::kStrip>::cbnd));
 		const int rc = sab_module_get(&ctx->modules, method, packed, k, lane_gap_constant(ctx, packed),
-					      kWidths[widx].smem, &fn, &occ, &err);
+					      smem, &fn, &occ, &err);
 		if (rc)
 			return fail(ctx, rc, "%s", err.c_str());
 		if (occ < 1)
 			return fail(ctx, SAB_ERR_CUDA, "kernel does not fit on an SM");
-		v.smem = kWidths[widx].smem;
+		v.smem = smem;
 		v.grid = occ * ctx->sm_count;
 		v.fn = fn;
 	}

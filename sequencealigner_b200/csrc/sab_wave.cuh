@@ -63,7 +63,32 @@ template <int K> struct WaveSmem {
 	int32_t ssub[kLetters * kLetters];
 	int desc[2][kWaveWarps][8]; // strip descriptors, parity = round & 1
 	int item;
+	uint2 cbnd[kGroup][32]; // kHoistExchange: the boundary rows a pair's FIRST strip starts from, (border V, -inf)
 };
+
+// Hoisted boundary exchange (NW and GA).  Left to itself the compiler re-derives the shared-window address of
+// the exchange buffer in every step of every warp -- S2R SR_CgaCtaId, LEA and a 6-instruction chain in front of
+// the boundary loads, again in front of the stores -- executes the 16 register moves of the "first strip"
+// constants whether the strip is a first one or not, and rebuilds the 64-bit address of the row letters from
+// g.  Here the three 32-bit shared addresses are formed once per kernel and made opaque (an empty asm), the
+// accesses are ld/st.shared with immediate row offsets, a pair's first strip reads its constant boundary from
+// shared memory (cbnd) like any other, the parity of the exchange buffer is an XOR on a uniform register and
+// the row pointer runs along.  ~45 of the ~165 bookkeeping instructions of a step and the S2R latency in front
+// of its first cell go away: C2 8.99 -> 9.16 TCUPS, C4 6.78 -> 7.17, same box (profiles/r2c_ab_hoist.txt).
+// SW got 0.9 % slower with it (three more live registers at 123 of 128): off there.
+#ifndef SAB_HOIST_METHODS
+#define SAB_HOIST_METHODS(method) ((method) != sab::M_SW)
+#endif
+template <int OFF> __device__ __forceinline__ uint2 lds64(const uint32_t a)
+{
+	uint2 v;
+	asm volatile("ld.shared.v2.u32 {%0, %1}, [%2+%3];" : "=r"(v.x), "=r"(v.y) : "r"(a), "n"(OFF) : "memory");
+	return v;
+}
+template <int OFF> __device__ __forceinline__ void sts64(const uint32_t a, const uint32_t x, const uint32_t y)
+{
+	asm volatile("st.shared.v2.u32 [%0+%1], {%2, %3};" ::"r"(a), "n"(OFF), "r"(x), "r"(y) : "memory");
+}
 
 // Per-launch constants of the cell update, in the lane format of VOps<PACKED>.
 template <int METHOD, bool PACKED> struct CellK {
@@ -194,6 +219,21 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 	const int v00 = METHOD == M_SW ? gA : 0;
 	const uint32_t VB = O::bcast(vb);
 	const int gS = METHOD == M_NW ? gA : gE; // score = V + gS * (Lq + Ls) for NW/GA
+	constexpr bool kHoistExchange = SAB_HOIST_METHODS(METHOD);
+	constexpr uint32_t kXchWarp = kGroup * 32 * sizeof(uint2); // one [warp] slab of xch
+	constexpr uint32_t kXchPar = (kWaveWarps - 1) * kXchWarp; // one parity of xch
+	uint32_t xin0 = 0, xout0 = 0, s_cbnd = 0; // shared-window addresses of my lane's first rows
+	if constexpr (kHoistExchange) {
+		const uint32_t s_xch =
+			(uint32_t)__cvta_generic_to_shared(&sm.xch[0][0][0][0]) + lane * (uint32_t)sizeof(uint2);
+		xin0 = s_xch + (warp ? warp - 1 : 0) * kXchWarp;
+		xout0 = s_xch + (warp < kWaveWarps - 1 ? warp : 0) * kXchWarp;
+		s_cbnd = (uint32_t)__cvta_generic_to_shared(&sm.cbnd[0][0]) + lane * (uint32_t)sizeof(uint2);
+		// opaque to the compiler, or it re-derives them from SR_CgaCtaId at every use (cheaper by its cost model)
+		asm volatile("" : "+r"(xin0), "+r"(xout0), "+r"(s_cbnd));
+		for (int i = tid; i < kGroup * 32; i += kWaveThreads)
+			(&sm.cbnd[0][0])[i] = make_uint2(VB, NEG); // visible after the item loop's first barrier
+	}
 
 	for (;;) {
 		__syncthreads(); // previous item fully done
@@ -309,6 +349,8 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 		uint32_t diag = 0, bestA = ck.ZERO, bestB = ck.ZERO;
 		const uint32_t *prof_s = sm.prof[0][warp][0];
 		const int T = R * G + (kWaveWarps - 1);
+		uint32_t xpar = 0; // kHoistExchange: (tau & 1) * kXchPar
+		const uint32_t *rowg = rowp; // kHoistExchange: rowp + g * kGroupWords * 32
 
 		for (int tau = 0; tau < T; tau++) {
 			if (tau_mod == 3 && tau_round + 1 < R)
@@ -352,8 +394,9 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 					if (!kPrefetchRows) {
 #pragma unroll
 						for (int i = 0; i < kGroupWords; i++)
-							w[i] = rowp[(g * kGroupWords + i) * 32];
+							w[i] = kHoistExchange ? rowg[i * 32] : rowp[(g * kGroupWords + i) * 32];
 					}
+					const uint32_t xout_a = xout0 + xpar;
 					const uint2 *xin = &sm.xch[(tau - 1) & 1][warp ? warp - 1 : 0][0][lane];
 					uint2 *xout = &sm.xch[tau & 1][warp < kWaveWarps - 1 ? warp : 0][0][lane];
 					const bool from_g = warp == 0, to_g = warp == kWaveWarps - 1;
@@ -362,6 +405,26 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 					auto run_rows = [&](auto nr_c, const int k0) {
 						constexpr int NR = decltype(nr_c)::value;
 						uint2 b[NR];
+						if constexpr (kHoistExchange) {
+						if (from_g && !first) {
+#pragma unroll
+							for (int k = 0; k < NR; k++)
+								b[k] = gfr[(r0 + k0 + k) * 32];
+						} else {
+							// a pair's first strip reads the constant rows, every other one what the
+							// warp to its left wrote in the previous step
+							const uint32_t a = (first ? s_cbnd : xin0 + (xpar ^ kXchPar)) + k0 * 32 * (uint32_t)sizeof(uint2);
+							static_assert(NR <= 8, "row block");
+							if (NR > 0) b[0] = lds64<0 * 256>(a);
+							if (NR > 1) b[1 % NR] = lds64<1 * 256>(a);
+							if (NR > 2) b[2 % NR] = lds64<2 * 256>(a);
+							if (NR > 3) b[3 % NR] = lds64<3 * 256>(a);
+							if (NR > 4) b[4 % NR] = lds64<4 * 256>(a);
+							if (NR > 5) b[5 % NR] = lds64<5 * 256>(a);
+							if (NR > 6) b[6 % NR] = lds64<6 * 256>(a);
+							if (NR > 7) b[7 % NR] = lds64<7 * 256>(a);
+						}
+						} else {
 						if (first) {
 #pragma unroll
 							for (int k = 0; k < NR; k++)
@@ -374,6 +437,7 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 #pragma unroll
 							for (int k = 0; k < NR; k++)
 								b[k] = xin[(k0 + k) * 32];
+						}
 						}
 						uint32_t ml[NR], x[NR], dg[NR], mprev[NR];
 						const uint32_t *pq[NR];
@@ -416,9 +480,21 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 								for (int k = 0; k < NR; k++)
 									gfr[(r0 + k0 + k) * 32] = make_uint2(ml[k], x[k]);
 							} else {
+								if constexpr (kHoistExchange) {
+								const uint32_t a = xout_a + k0 * 32 * (uint32_t)sizeof(uint2);
+								if (NR > 0) sts64<0 * 256>(a, ml[0], x[0]);
+								if (NR > 1) sts64<1 * 256>(a, ml[1 % NR], x[1 % NR]);
+								if (NR > 2) sts64<2 * 256>(a, ml[2 % NR], x[2 % NR]);
+								if (NR > 3) sts64<3 * 256>(a, ml[3 % NR], x[3 % NR]);
+								if (NR > 4) sts64<4 * 256>(a, ml[4 % NR], x[4 % NR]);
+								if (NR > 5) sts64<5 * 256>(a, ml[5 % NR], x[5 % NR]);
+								if (NR > 6) sts64<6 * 256>(a, ml[6 % NR], x[6 % NR]);
+								if (NR > 7) sts64<7 * 256>(a, ml[7 % NR], x[7 % NR]);
+								} else {
 #pragma unroll
 								for (int k = 0; k < NR; k++)
 									xout[(k0 + k) * 32] = make_uint2(ml[k], x[k]);
+								}
 							}
 						}
 					};
@@ -509,7 +585,11 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 					g = 0;
 					rho++;
 				}
+				if (kHoistExchange)
+					rowg = g ? rowg + kGroupWords * 32 : rowp;
 			}
+			if (kHoistExchange)
+				xpar ^= kXchPar;
 			u++;
 			if (++tau_mod == G) {
 				tau_mod = 0;

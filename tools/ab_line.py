@@ -11,6 +11,6 @@ if not lines:
 d = json.loads(lines[-1])
 r = d.get("roofline") or {}
 print(label, "|", d["config"]["workload"][:48],
-      "value=%.0f e2e=%.0f frac=%.3f kernel/gpu=%.0f widths=%s" %
+      "value=%.0f e2e=%.0f frac=%.3f kernel/gpu=%.0f widths=%s checksum=%s" %
       (d["value"], d["e2e"]["value"], r.get("frac") or 0, r.get("gcups_kernel_per_gpu") or 0,
-       d.get("width_launches")))
+       d.get("width_launches"), d["e2e"].get("checksum")))
