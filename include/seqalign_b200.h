@@ -335,6 +335,39 @@ int sab_parse_dsv(uint8_t *file, size_t bytes, uint8_t delimiter, int32_t seq_co
  * sab_parse_* (src/io/input.c:70-81).  Returns the store's size in bytes (terminators included). */
 int64_t sab_build_meta(const uint8_t *seqs, int32_t num, sab_meta *meta);
 
+/*
+ * No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * Smith-Waterman scores (src/bio/method/sw.c:15-61 arithmetic, int32) of a caller-given list of pairs,
+ * computed WITHOUT any allocation: no cudaMalloc / cudaFree / cudaHostAlloc, no allocating library call, no
+ * host <-> device copy.  Every buffer is a DEVICE buffer of the current device, owned by the caller:
+ *   d_seqs, d_meta   device copies of struct input's `seqs` / `meta` (src/io/input.h:6-11), `num` sequences,
+ *                    none longer than `max_len`
+ *   d_pair_i/j       `count` pairs of sequence indices (i != j, either order)
+ *   d_scores         out: d_scores[k] = score(d_pair_i[k], d_pair_j[k]) -- what sab_align writes to
+ *                    matrix[j(j-1)/2 + i]; INT32_MIN for a bad index, a length outside 1..max_len or a letter
+ *                    outside the matrix alphabet
+ * cfg: method must be SAB_SW; gap_open, gap_ext, seq_lut, sub_mat as for sab_create (device, panel, flags
+ * unused).  The kernel is enqueued on `stream` (a cudaStream_t; NULL = the default stream) and the call
+ * returns without waiting for it, like a kernel launch.
+ *
+ * The kernel's scratch (two DP rows per thread) is ONE file-scope device array of SAB_NOALLOC_SCRATCH_BYTES
+ * that every GPU which loads the library holds until exit.  Limit: max_len <= SAB_NOALLOC_MAX_LEN, beyond it
+ * SAB_ERR_ARG and a message in `err` (use sab_align).  All calls on a device share that array: calls that
+ * OVERLAP on one GPU (two streams, concurrent replays of a captured graph) race on it and must be serialised
+ * by the caller; calls on one stream are ordered and safe.  The array keeps the previous call's contents;
+ * nothing in it needs to start at zero (every thread writes a pair's border row before reading it).
+ * The first call on a device looks the array's address up (cudaGetSymbolAddress: may load the library's
+ * device code); a call with count == 0 does only that -- make it once per device before capturing a graph.
+ * One thread per pair: meant for lists of pairs, not for all-vs-all throughput.
+ */
+#define SAB_NOALLOC_SCRATCH_BYTES (16u << 20)
+#define SAB_NOALLOC_MAX_LEN 4095
+int sab_sw_pairs_noalloc(const sab_config *cfg, const uint8_t *d_seqs, const sab_meta *d_meta, int32_t num,
+			 int32_t max_len, const int32_t *d_pair_i, const int32_t *d_pair_j, int64_t count,
+			 int32_t *d_scores, void *stream, char *err, size_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -14,7 +14,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libseqalign_b200.so"
 PIPE_LIB = PKG / "libsab_pipepeak.so"
-SOURCES = ["sab_capi.cu", "sab_module.cu", "sab_filter.cu", "sab_tables.cpp", "sab_h5.cpp", "sab_source.cpp"]
+SOURCES = ["sab_capi.cu", "sab_module.cu", "sab_filter.cu", "sab_tables.cpp", "sab_h5.cpp", "sab_source.cpp", "sab_noalloc.cu"]
 # the strip kernel: one cubin per register-strip width (-DSAB_K=<columns>), embedded in the library and
 # loaded by sab_module.cu, which overwrites the placeholder immediate below with the job's gap constant
 WAVE_INST = "sab_wave_inst.cu"

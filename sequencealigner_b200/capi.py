@@ -13,6 +13,8 @@ from .build import LIB
 
 SAB_OK = 0
 SAB_ERR_PARSE = -7
+SAB_NOALLOC_SCRATCH_BYTES = 16 << 20
+SAB_NOALLOC_MAX_LEN = 4095
 SAB_SRC_NONE, SAB_SRC_FASTA, SAB_SRC_DSV = 0, 1, 2
 SAB_NW, SAB_GA, SAB_SW = 0, 1, 2
 SAB_FLAG_FORCE_INT32 = 1
@@ -118,6 +120,9 @@ SYMBOLS = {
                                 C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_int32),
                                 C.POINTER(C.c_int32), C.c_char_p, C.c_size_t]),
     "sab_build_meta": (C.c_int64, [C.c_void_p, C.c_int32, C.POINTER(SabMeta)]),
+    "sab_sw_pairs_noalloc": (C.c_int, [C.POINTER(SabConfig), C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                       C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_char_p,
+                                       C.c_size_t]),
 }
 
 _lib = None
