@@ -89,6 +89,23 @@ template <int OFF> __device__ __forceinline__ void sts64(const uint32_t a, const
 {
 	asm volatile("st.shared.v2.u32 [%0+%1], {%2, %3};" ::"r"(a), "n"(OFF), "r"(x), "r"(y) : "memory");
 }
+constexpr int kXchRowBytes = 32 * sizeof(uint2); // one row of the exchange buffer: a uint2 per lane
+// rows k = 0 .. NR-1 of my lane, starting at shared address a
+template <int NR, int k = 0> __device__ __forceinline__ void lds_rows(const uint32_t a, uint2 (&b)[NR])
+{
+	if constexpr (k < NR) {
+		b[k] = lds64<k * kXchRowBytes>(a);
+		lds_rows<NR, k + 1>(a, b);
+	}
+}
+template <int NR, int k = 0>
+__device__ __forceinline__ void sts_rows(const uint32_t a, const uint32_t (&v)[NR], const uint32_t (&x)[NR])
+{
+	if constexpr (k < NR) {
+		sts64<k * kXchRowBytes>(a, v[k], x[k]);
+		sts_rows<NR, k + 1>(a, v, x);
+	}
+}
 
 // Per-launch constants of the cell update, in the lane format of VOps<PACKED>.
 template <int METHOD, bool PACKED> struct CellK {
@@ -406,26 +423,16 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 						constexpr int NR = decltype(nr_c)::value;
 						uint2 b[NR];
 						if constexpr (kHoistExchange) {
-						if (from_g && !first) {
+							if (from_g && !first) {
 #pragma unroll
-							for (int k = 0; k < NR; k++)
-								b[k] = gfr[(r0 + k0 + k) * 32];
-						} else {
-							// a pair's first strip reads the constant rows, every other one what the
-							// warp to its left wrote in the previous step
-							const uint32_t a = (first ? s_cbnd : xin0 + (xpar ^ kXchPar)) + k0 * 32 * (uint32_t)sizeof(uint2);
-							static_assert(NR <= 8, "row block");
-							if (NR > 0) b[0] = lds64<0 * 256>(a);
-							if (NR > 1) b[1 % NR] = lds64<1 * 256>(a);
-							if (NR > 2) b[2 % NR] = lds64<2 * 256>(a);
-							if (NR > 3) b[3 % NR] = lds64<3 * 256>(a);
-							if (NR > 4) b[4 % NR] = lds64<4 * 256>(a);
-							if (NR > 5) b[5 % NR] = lds64<5 * 256>(a);
-							if (NR > 6) b[6 % NR] = lds64<6 * 256>(a);
-							if (NR > 7) b[7 % NR] = lds64<7 * 256>(a);
-						}
-						} else {
-						if (first) {
+								for (int k = 0; k < NR; k++)
+									b[k] = gfr[(r0 + k0 + k) * 32];
+							} else {
+								// a pair's first strip reads the constant rows, every other one
+								// what the warp to its left wrote in the previous step
+								lds_rows<NR>((first ? s_cbnd : xin0 + (xpar ^ kXchPar)) + k0 * kXchRowBytes, b);
+							}
+						} else if (first) {
 #pragma unroll
 							for (int k = 0; k < NR; k++)
 								b[k] = make_uint2(VB, NEG);
@@ -437,7 +444,6 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 #pragma unroll
 							for (int k = 0; k < NR; k++)
 								b[k] = xin[(k0 + k) * 32];
-						}
 						}
 						uint32_t ml[NR], x[NR], dg[NR], mprev[NR];
 						const uint32_t *pq[NR];
@@ -481,19 +487,11 @@ __global__ void __launch_bounds__(kWaveThreads, MINB) sab_wave_kernel(const Tile
 									gfr[(r0 + k0 + k) * 32] = make_uint2(ml[k], x[k]);
 							} else {
 								if constexpr (kHoistExchange) {
-								const uint32_t a = xout_a + k0 * 32 * (uint32_t)sizeof(uint2);
-								if (NR > 0) sts64<0 * 256>(a, ml[0], x[0]);
-								if (NR > 1) sts64<1 * 256>(a, ml[1 % NR], x[1 % NR]);
-								if (NR > 2) sts64<2 * 256>(a, ml[2 % NR], x[2 % NR]);
-								if (NR > 3) sts64<3 * 256>(a, ml[3 % NR], x[3 % NR]);
-								if (NR > 4) sts64<4 * 256>(a, ml[4 % NR], x[4 % NR]);
-								if (NR > 5) sts64<5 * 256>(a, ml[5 % NR], x[5 % NR]);
-								if (NR > 6) sts64<6 * 256>(a, ml[6 % NR], x[6 % NR]);
-								if (NR > 7) sts64<7 * 256>(a, ml[7 % NR], x[7 % NR]);
+									sts_rows<NR>(xout_a + k0 * kXchRowBytes, ml, x);
 								} else {
 #pragma unroll
-								for (int k = 0; k < NR; k++)
-									xout[(k0 + k) * 32] = make_uint2(ml[k], x[k]);
+									for (int k = 0; k < NR; k++)
+										xout[(k0 + k) * 32] = make_uint2(ml[k], x[k]);
 								}
 							}
 						}
