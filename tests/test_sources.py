@@ -176,3 +176,31 @@ def test_live_byte_soups_against_the_reference_binary(oracle_mod):
             assert kind == "error" and same_error(got, r["error"]), (name, data, got, r)
         checked += 1
     assert checked >= 100
+
+
+def test_live_long_lines_and_mixed_line_ends_against_the_reference_binary(oracle_mod):
+    """The FASTA block-copy path: records of up to 400 letters in lines of 1..120, LF / CRLF / CR-only line
+    ends, lower case, then up to three byte edits -- both parsers must agree on every file."""
+    if not oracle_mod.ref_available():
+        pytest.skip("oracle/_ref/seqalign not built")
+    rng = np.random.default_rng(77)
+    edits = [b">", b"\n", b"\r", b"\r\n", b" ", b"J", b"\0", b"\xe9", b"", b"", b"a", b"\t", b"\n\n", b"\r\r", b">x"]
+    for matrix, alpha in (("blosum62", b"ACDEFGHIKLMNPQRSTVWYacdw"), ("nuc44", b"ACGTacgtNn")):
+        letters = np.frombuffer(alpha, np.uint8)
+        for _ in range(120):
+            eol = [b"\n", b"\r\n", b"\r"][int(rng.integers(0, 3))] if rng.random() < .5 else b"\n"
+            recs = []
+            for r in range(int(rng.integers(2, 5))):
+                s = letters[rng.integers(0, letters.size, int(rng.integers(1, 400)))].tobytes()
+                w = int(rng.integers(1, 120))
+                recs.append(b">r%d" % r + eol + eol.join(s[i:i + w] for i in range(0, len(s), w)))
+            data = eol.join(recs) + (eol if rng.random() < .6 else b"")
+            for _ in range(int(rng.choice([0, 1, 1, 2, 3]))):
+                at = int(rng.integers(0, len(data) + 1))
+                data = data[:at] + edits[int(rng.integers(0, len(edits)))] + data[at + int(rng.integers(0, 2)):]
+            r = oracle_mod.reference_parse(data, "fa", matrix=matrix)
+            kind, got = ours("fa", data, {"matrix": matrix})
+            if r["seqs"] is not None:
+                assert kind == "seqs" and got == [s.decode("latin-1") for s in r["seqs"]], (data, got, r)
+            else:
+                assert kind == "error" and got == r["error"], (data, got, r)
