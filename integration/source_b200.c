@@ -65,23 +65,20 @@ static enum parse_result dsv_b200(struct source src, struct input *in)
 	const size_t bytes = (size_t)(src.fend - src.file);
 	char msg[128] = "";
 	s32 cols = 0, seq_col = -1;
-	char *names = malloc(bytes + 1);
-	if (!names) {
-		perr("Out of memory during DSV parsing");
-		return PARSER_ERROR;
-	}
-	int rc = sab_dsv_header(src.file, bytes, delim, &cols, &seq_col, names, bytes + 1, msg, sizeof(msg));
-	if (rc != SAB_OK) {
-		free(names);
+	int rc = sab_dsv_header(src.file, bytes, delim, &cols, &seq_col, nullptr, 0, msg, sizeof(msg));
+	if (rc != SAB_OK)
 		return finish(rc, msg, in, 0, 0, "DSV");
-	}
 
 	int first_row_is_data = 0;
 	if (seq_col < 0) {
-		/* nobody named the column: ask, outside the timed input phase (dsv.c:146-160) */
+		/* nobody named the column: ask, outside the timed input phase (dsv.c:146-160).  Only now are the
+		 * first row's field texts needed (they cannot be longer than the file) */
+		char *names = malloc(bytes + 1);
 		const char **list = malloc(sizeof(*list) * ((size_t)cols + 1));
-		if (!list) {
+		if (!names || !list ||
+		    sab_dsv_header(src.file, bytes, delim, &cols, &seq_col, names, bytes + 1, msg, sizeof(msg)) != SAB_OK) {
 			free(names);
+			free(list);
 			perr("Out of memory during DSV parsing");
 			return PARSER_ERROR;
 		}
@@ -103,9 +100,9 @@ static enum parse_result dsv_b200(struct source src, struct input *in)
 		}
 		bench_input_start();
 		free(list);
+		free(names);
 		seq_col = pick;
 	}
-	free(names);
 
 	s32 num = 0, longest = 0;
 	rc = sab_parse_dsv(src.file, bytes, delim, seq_col, first_row_is_data, (const int32_t *)SEQ_LUT, GAP_PEN,

@@ -138,12 +138,14 @@ def parse_source(data: bytes, ext: str, seq_lut, gap_pen: int = 0, column: int |
                                  C.byref(longest), err, len(err))
     else:
         cols, found = C.c_int32(0), C.c_int32(-1)
-        names = C.create_string_buffer(len(data) + 1)
         rc = lib.sab_dsv_header(buf.ctypes.data, len(data), delim, C.byref(cols), C.byref(found),
-                                names, len(names), err, len(err))
+                                None, 0, err, len(err))
         if rc == capi.SAB_OK:
             if column is None:
                 if found.value < 0:
+                    names = C.create_string_buffer(len(data) + 1)  # the first row's field texts
+                    lib.sab_dsv_header(buf.ctypes.data, len(data), delim, C.byref(cols), C.byref(found),
+                                       names, len(names), err, len(err))
                     shown = names.raw.split(b"\0")[:cols.value]
                     raise ParseError("no column is named like a sequence column; pass column= "
                                      f"(and header=False if the first row is data): {shown}")
